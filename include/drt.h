@@ -1,0 +1,166 @@
+/* drt.h -- C ABI of the B200-native path-tracing hot path (libdrt.so).
+ *
+ * Drop-in boundary for the de-facto library surface of LightShade12/DustRayTracer (the reference has
+ * no formal FFI; its only caller is the editor, DustRayTracer/src/Editor/EditorLayer.cpp:35-55,317-318,424).
+ * Each entry point names the reference interface it replaces. Plain pointers and sizes only; every
+ * function returns 0 on success or a negative drt_status, and drt_last_error() gives the message of the
+ * calling thread's last failure (the reference prints and exit(99)s: Editor/Common/CudaCommon.cu:4-13).
+ * There is no CPU fallback: every call that touches the device fails with DRT_ERR_CUDA without one.
+ */
+#ifndef DRT_H
+#define DRT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct drt_scene drt_scene;       /* replaces struct Scene            (Core/Scene/Scene.cuh:41-57) */
+typedef struct drt_renderer drt_renderer; /* replaces class Renderer          (Core/Renderer.hpp:14-47)    */
+
+typedef enum drt_status {
+	DRT_OK = 0,
+	DRT_ERR_INVALID = -1, /* bad argument / call order */
+	DRT_ERR_IO = -2,      /* file missing or unreadable */
+	DRT_ERR_FORMAT = -3,  /* malformed glTF / image */
+	DRT_ERR_CUDA = -4,    /* CUDA runtime error (message carries cudaGetErrorString) */
+	DRT_ERR_NOMEM = -5
+} drt_status;
+
+/* Field-for-field the reference's Camera POD (Core/Scene/Camera.cuh:32-46), 88 bytes. */
+typedef struct drt_camera {
+	float exposure;        /* 1 */
+	float vfov_rad;        /* deg2rad(60) */
+	float zfar, znear;     /* unused by the path, kept for layout */
+	float aspect_ratio;    /* m_AspectRatio, unused */
+	float defocus_angle;   /* degrees; <= 0 disables the thin lens */
+	float focus_dist;      /* 10 */
+	float movement_speed;  /* host fly-cam only */
+	float position[3];     /* (0,2,5) */
+	float forward_dir[3];  /* (0,0,-1) */
+	float up_dir[3];       /* host fly-cam only */
+	float right_dir[3];    /* host fly-cam only */
+	uint32_t viewheight, viewwidth;
+} drt_camera;
+
+/* Field-for-field the reference's RendererSettings (Core/Scene/RendererSettings.h:22-34), 64 bytes. */
+typedef struct drt_settings {
+	uint8_t gamma_correction; /* true */
+	uint8_t tone_mapping;     /* true */
+	uint8_t enable_sunlight;  /* false */
+	uint8_t _pad0;
+	int32_t max_samples;      /* 500: rendering stops when the frame index reaches it (Renderer.cu:82) */
+	int32_t ray_bounce_limit; /* 2: path segments = limit + 1 */
+	int32_t render_mode;      /* 0 NORMALMODE, 1 DEBUGMODE */
+	int32_t debug_mode;       /* 0 albedo, 1 normal, 2 barycentric, 3 uvs, 4 mesh-bvh heat, 5 world-bvh */
+	int32_t _pad1;
+	float sunlight_dir[2];    /* radians (-0.803, 0.681) */
+	float sunlight_color[3];
+	float sunlight_intensity; /* 30 */
+	float sky_color[3];
+	float sky_intensity;      /* 20 */
+} drt_settings;
+
+/* Field-for-field the reference's Material (Core/Scene/Material.cuh:4-23), 44 bytes. */
+typedef struct drt_material {
+	float albedo[3];
+	float emissive_factor[3];
+	int32_t albedo_texture_index; /* -1: none. Indexes IMAGES, like the reference (Scene.cu:79, RayGen.cuh:117) */
+	float roughness;
+	uint8_t transmission, _pad0[3];
+	float refractive_index;
+	uint8_t metallic, _pad1[3];
+} drt_material;
+
+typedef struct drt_bvh_params {
+	int32_t bin_count;   /* informational: the GPU builder uses 16 bins (8 for small nodes); ref m_BinCount = 8 */
+	int32_t leaf_target; /* informational: wide-node leaf slots hold <= 3 triangles; ref m_TargetLeafPrimitivesCount */
+	int32_t reserved[6];
+} drt_bvh_params;
+
+typedef struct drt_scene_stats {
+	uint64_t triangles, materials, textures, meshes;
+	uint64_t wide_nodes, bvh2_nodes, bvh_levels;
+	uint64_t device_bytes;   /* nodes + triangles + shading records + textures resident in HBM */
+	double build_ms;         /* device time of the last drt_scene_build_bvh */
+	double load_ms;
+} drt_scene_stats;
+
+typedef struct drt_hit {
+	int32_t prim_id; /* canonical id = index of the triangle in load order; -1 = miss */
+	float t, u, v;   /* hit distance and barycentrics (UVW = (1-u-v, u, v), Intersection.cu:31) */
+} drt_hit;
+
+typedef struct drt_counters {
+	uint64_t closest_rays; /* TraceRay calls  (Kernel/TraceRay.cu:15) */
+	uint64_t shadow_rays;  /* RayTest calls   (Kernel/TraceRay.cu:35) */
+	uint64_t node_visits, tri_tests, tie_events, alpha_tests, max_stack, texel_clamps; /* stats launches only */
+} drt_counters;
+
+typedef enum drt_format {
+	DRT_RGBA32F = 0,      /* display buffer: acc / samples, a = 1   (what the reference writes to its GL surface) */
+	DRT_RGBA8 = 1,        /* display buffer clamped to 8 bit          (what the editor's "save png" reads back)   */
+	DRT_ACCUM_RGB32F = 2  /* raw accumulation sums, 3 floats / pixel  (the reference's float3 buffer)              */
+} drt_format;
+
+typedef enum drt_flags {
+	DRT_FLAG_STRICT = 1,       /* separately-rounded fp32 in the reference's operation order (parity mode)      */
+	DRT_FLAG_HOST_ARG_ORDER = 2, /* draw randomUnitVec3 components right-to-left like the g++-compiled oracle     */
+	DRT_FLAG_STATS = 4         /* count node visits / triangle tests (slower; for the roofline's V and T terms) */
+} drt_flags;
+
+/* ---- scene: replaces Scene::loadGLTFmodel (Scene.cu:181-317) and BVHBuilder::build* (BVHBuilder.cu:11-145) ---- */
+int drt_scene_load_gltf(const char* path, drt_scene** out);
+/* Synthetic soups: pos 9 floats/tri, uv 6 floats/tri or NULL, material index per tri or NULL. */
+int drt_scene_from_triangles(const float* pos, const float* uv, const int32_t* material_index, size_t n_tris,
+	const drt_material* materials, size_t n_materials, drt_scene** out);
+/* Appends an 8-bit texture (comps = 1..4) to a scene made by drt_scene_from_triangles. */
+int drt_scene_add_texture(drt_scene* scene, int32_t width, int32_t height, int32_t comps, const uint8_t* pixels);
+int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* params_or_null, int device);
+int drt_scene_get_stats(const drt_scene* scene, drt_scene_stats* out);
+/* Host copy of the triangle soup in load order, in the reference's 128-byte Triangle layout (Triangle.cuh:7-19). */
+int drt_scene_get_triangles(const drt_scene* scene, void* out, size_t bytes);
+int drt_scene_get_materials(const drt_scene* scene, drt_material* out, size_t count);
+int drt_scene_get_texture(const drt_scene* scene, int32_t index, int32_t* width, int32_t* height, int32_t* comps,
+	uint8_t* pixels_or_null, size_t bytes);
+/* Device-built tree for inspection: 80-byte wide nodes and 48-byte leaf-order triangle records. */
+int drt_scene_get_wide_nodes(const drt_scene* scene, void* out, size_t bytes);
+int drt_scene_get_leaf_triangles(const drt_scene* scene, void* out, size_t bytes);
+void drt_scene_destroy(drt_scene* scene);
+
+/* ---- renderer: replaces Renderer::{ResizeBuffer,Render,resetAccumulationBuffer,getSampleCount} (Renderer.cu:29-136) ---- */
+int drt_renderer_create(int device, drt_renderer** out);
+int drt_renderer_set_stream(drt_renderer* r, void* cuda_stream); /* launch on a caller-owned stream (NULL = own stream) */
+int drt_renderer_set_flags(drt_renderer* r, uint32_t flags);
+/* Sample-range sharding across GPUs: this renderer renders frame indices first, first+stride, ... (default 1, 1). */
+int drt_renderer_set_frame_schedule(drt_renderer* r, uint32_t first_frame, uint32_t stride);
+int drt_renderer_resize(drt_renderer* r, uint32_t width, uint32_t height);
+/* Renders up to n_samples further samples in one batch (the reference renders one per call) and updates the
+ * display buffer; stops at settings->max_samples like Renderer.cu:82. ms = device time of the launch(es). */
+int drt_renderer_render(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, const drt_settings* settings,
+	uint32_t n_samples, float* ms_or_null);
+int drt_renderer_reset(drt_renderer* r);
+uint32_t drt_renderer_sample_count(const drt_renderer* r); /* the reference's m_FrameIndex: samples done + 1 */
+uint32_t drt_renderer_width(const drt_renderer* r);
+uint32_t drt_renderer_height(const drt_renderer* r);
+int drt_renderer_readback(drt_renderer* r, drt_format format, void* host, size_t bytes);
+/* Device pointer of the W*H float4 accumulation buffer (for an NCCL reduce over NVLink) and the sample total
+ * the display divides by; drt_renderer_resolve recomputes the display buffer after an external reduce. */
+int drt_renderer_accum_device_ptr(drt_renderer* r, void** ptr, size_t* bytes);
+int drt_renderer_resolve(drt_renderer* r, uint32_t total_samples);
+int drt_renderer_get_counters(drt_renderer* r, drt_counters* out, int reset);
+/* Parity probe: primary rays exactly as the path issues them for `frame_index`, closest hit only. */
+int drt_trace_primary(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, uint32_t frame_index,
+	drt_hit* out_host, size_t count);
+
+void drt_default_camera(drt_camera* out);     /* Camera.cuh:32-46 + EditorLayer.cpp:35-40 */
+void drt_default_settings(drt_settings* out); /* RendererSettings.h:22-34 */
+const char* drt_last_error(void);
+const char* drt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DRT_H */

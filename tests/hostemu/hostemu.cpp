@@ -1,0 +1,310 @@
+// tests/hostemu/hostemu.cpp -- TEST INFRASTRUCTURE ONLY. Never linked into libdrt.so and never on a
+// product path: libdrt.so has no CPU fallback and fails loudly without a CUDA device.
+//
+// The build container has no GPU, so the per-thread bodies of the device code (drt_*.cuh, written as
+// __host__ __device__ functions) are compiled here as plain C++ and driven by serial / OpenMP loops.
+// This lets the `-m "not gpu"` tests check the LOGIC of the kernels (builder passes, wide-node
+// traversal, shading loop, RNG stream) against the reference oracle before any GPU time is spent.
+// The real kernels (drt_kernels.cu) call the very same functions.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#include "../../dustraytracer_b200/csrc/drt_host.h"
+#include "../../dustraytracer_b200/csrc/drt_params.h"
+#include "../../dustraytracer_b200/csrc/drt_build_driver.h"
+
+using namespace drt;
+
+namespace drt {
+static thread_local std::string g_err;
+void set_error(const std::string& m) { g_err = m; }
+}
+
+namespace {
+
+struct EmuExec : BuildExec {
+	int launch(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n) override
+	{
+		for (int i = 0; i < n; i++) {
+			switch (pass) {
+			case PASS_PRIM_BOUNDS: prim_bounds(A, i); break;
+			case PASS_INIT_BINS: init_bin_word(A, i, a); break;
+			case PASS_BIN: bin_prim(A, i); break;
+			case PASS_SPLIT: split_node(A, i); break;
+			case PASS_PARTITION: partition_prim(A, i); break;
+			case PASS_COLLAPSE: collapse_node(A, idx_final, a, b, i); break;
+			}
+		}
+		return 0;
+	}
+	int read_state(const BuildArrays& A, BuildState& out) override { out = *A.state; return 0; }
+	int write_state(const BuildArrays& A, const BuildState& in) override { *A.state = in; return 0; }
+	int write_root(const BuildArrays& A, const BuildNode& root, const BuildSplit& split) override
+	{
+		A.nodes[0] = root; A.splits[0] = split; A.wide_src[0] = 0;
+		return 0;
+	}
+};
+
+struct EmuScene {
+	HostScene host;
+	std::vector<int32_t> mat_flags;
+	std::vector<drt_f4> tri_lo, tri_hi, out_tris, out_shade, materials;
+	std::vector<int> idx0, idx1, pn0, pn1, bins, wide_src;
+	std::vector<BuildNode> nodes;
+	std::vector<BuildSplit> splits;
+	std::vector<WideNode> wide;
+	std::vector<TexDesc> texdesc;
+	std::vector<uint32_t> texels;
+	BuildState state;
+	BuildResult result;
+	SceneView view;
+};
+
+void upload_tables(EmuScene* s)
+{
+	const HostScene& h = s->host;
+	// textures: RGBA8 pool (same packing as the device upload in drt_api.cu)
+	for (const HostTexture& t : h.textures) {
+		TexDesc d;
+		d.offset = (uint32_t)s->texels.size(); d.width = t.width; d.height = t.height; d.comps = t.comps;
+		size_t np = (size_t)t.width * t.height;
+		for (size_t p = 0; p < np; p++) {
+			const uint8_t* px = t.pixels.data() + p * t.comps;
+			uint32_t r = px[0], g = t.comps >= 3 ? px[1] : px[0], b = t.comps >= 3 ? px[2] : px[0];
+			uint32_t a = t.comps == 4 ? px[3] : (t.comps == 2 ? px[1] : 255u);
+			s->texels.push_back(r | (g << 8) | (b << 16) | (a << 24));
+		}
+		s->texdesc.push_back(d);
+	}
+	size_t nm = h.materials.size();
+	s->materials.resize(nm + 1);
+	for (size_t i = 0; i <= nm; i++) {
+		drt_f4 m;
+		if (i < nm) {
+			int tex = h.materials[i].albedo_texture_index;
+			if (tex >= (int)h.textures.size()) tex = -1;
+			m.x = h.materials[i].albedo[0]; m.y = h.materials[i].albedo[1]; m.z = h.materials[i].albedo[2];
+			m.w = as_float((uint32_t)tex);
+		}
+		else { m.x = m.y = m.z = 1.f; m.w = as_float((uint32_t)-1); } // default material for index -1
+		s->materials[i] = m;
+	}
+	size_t n = h.tri_count();
+	s->mat_flags.resize(n);
+	for (size_t i = 0; i < n; i++) {
+		int mi = h.mat[i];
+		if (mi < 0 || (size_t)mi >= nm) mi = (int)nm;
+		uint32_t flag = 0;
+		if ((size_t)mi < nm) {
+			int tex = h.materials[mi].albedo_texture_index;
+			if (tex >= 0 && tex < (int)h.textures.size() && h.textures[tex].comps == 4) flag = 0x80000000u;
+		}
+		s->mat_flags[i] = (int32_t)((uint32_t)mi | flag);
+	}
+}
+
+int build(EmuScene* s)
+{
+	upload_tables(s);
+	const int n = (int)s->host.tri_count();
+	s->tri_lo.resize(n); s->tri_hi.resize(n);
+	s->out_tris.resize(3 * (size_t)n + 3); s->out_shade.resize(3 * (size_t)n + 3);
+	s->idx0.resize(n); s->idx1.resize(n); s->pn0.resize(n); s->pn1.resize(n);
+	s->nodes.resize(2 * (size_t)n + 2); s->splits.resize(2 * (size_t)n + 2);
+	s->wide.resize((size_t)n + 1); s->wide_src.resize((size_t)n + 1);
+	s->bins.resize(build_bin_slots_capacity(n) * 3 * DRT_BINS * DRT_BIN_WORDS);
+	BuildArrays A;
+	memset(&A, 0, sizeof(A));
+	A.pos = s->host.pos.data(); A.uv = s->host.uv.data(); A.fnormal = s->host.fnormal.data(); A.mat = s->mat_flags.data();
+	A.n = n;
+	A.tri_lo = s->tri_lo.data(); A.tri_hi = s->tri_hi.data();
+	A.idx_in = s->idx0.data(); A.idx_out = s->idx1.data(); A.pnode_in = s->pn0.data(); A.pnode_out = s->pn1.data();
+	A.nodes = s->nodes.data(); A.splits = s->splits.data(); A.bins = s->bins.data(); A.state = &s->state;
+	A.wide_src = s->wide_src.data(); A.wide = s->wide.data(); A.out_tris = s->out_tris.data(); A.out_shade = s->out_shade.data();
+	EmuExec ex;
+	int rc = run_build(ex, A, s->result);
+	SceneView& v = s->view;
+	v.nodes = (const drt_u4*)s->wide.data();
+	v.tris = s->out_tris.data(); v.shade = s->out_shade.data(); v.materials = s->materials.data();
+	v.textures = s->texdesc.data(); v.texels = s->texels.data();
+	v.num_tris = n; v.num_nodes = s->result.wide_nodes; v.num_materials = (int)s->materials.size(); v.num_textures = (int)s->texdesc.size();
+	return rc;
+}
+
+} // namespace
+
+extern "C" {
+
+const char* emu_last_error() { return g_err.c_str(); }
+
+void* emu_scene_load(const char* path)
+{
+	EmuScene* s = new EmuScene();
+	std::string err;
+	if (load_gltf(path, s->host, err) != 0) { g_err = err; delete s; return nullptr; }
+	if (build(s) != 0) { g_err = "build failed"; delete s; return nullptr; }
+	return s;
+}
+
+void* emu_scene_from_triangles(const float* pos, const float* uv, const int32_t* mat, int n, const drt_material* mats, int nm)
+{
+	EmuScene* s = new EmuScene();
+	HostScene& h = s->host;
+	h.pos.assign(pos, pos + 9 * (size_t)n);
+	if (uv) h.uv.assign(uv, uv + 6 * (size_t)n); else h.uv.assign(6 * (size_t)n, 0.f);
+	h.vnormal.assign(9 * (size_t)n, 0.f);
+	h.fnormal.resize(3 * (size_t)n);
+	for (int i = 0; i < n; i++) {
+		float zero9[9] = { 0 };
+		compute_face_normal(pos + 9 * (size_t)i, zero9, h.fnormal.data() + 3 * (size_t)i);
+		h.mat.push_back(mat ? mat[i] : 0);
+	}
+	for (int i = 0; i < nm; i++) h.materials.push_back(mats[i]);
+	if (build(s) != 0) { delete s; return nullptr; }
+	return s;
+}
+
+void emu_scene_free(void* h) { delete (EmuScene*)h; }
+
+// info[0..7] = tris, materials, textures, wide nodes, bvh2 nodes, levels, wide levels, tris emitted
+void emu_scene_info(void* h, long long* info)
+{
+	EmuScene* s = (EmuScene*)h;
+	info[0] = (long long)s->host.tri_count(); info[1] = (long long)s->host.materials.size(); info[2] = (long long)s->host.textures.size();
+	info[3] = s->result.wide_nodes; info[4] = s->result.bvh2_nodes; info[5] = s->result.levels; info[6] = s->result.wide_levels;
+	info[7] = s->result.tris_emitted;
+}
+
+// Triangle soup in load order in the reference's 128-byte layout (padding word zeroed).
+void emu_scene_get_triangles(void* h, float* out)
+{
+	const HostScene& s = ((EmuScene*)h)->host;
+	for (size_t i = 0; i < s.tri_count(); i++) {
+		float* o = out + 32 * i;
+		const float* p = &s.pos[9 * i]; const float* n = &s.vnormal[9 * i]; const float* t = &s.uv[6 * i];
+		o[0] = (p[0] + p[3] + p[6]) / 3; o[1] = (p[1] + p[4] + p[7]) / 3; o[2] = (p[2] + p[5] + p[8]) / 3; o[3] = 0;
+		for (int k = 0; k < 3; k++) {
+			float* v = o + 4 + 8 * k;
+			v[0] = p[3 * k]; v[1] = p[3 * k + 1]; v[2] = p[3 * k + 2];
+			v[3] = n[3 * k]; v[4] = n[3 * k + 1]; v[5] = n[3 * k + 2];
+			v[6] = t[2 * k]; v[7] = t[2 * k + 1];
+		}
+		o[28] = s.fnormal[3 * i]; o[29] = s.fnormal[3 * i + 1]; o[30] = s.fnormal[3 * i + 2];
+		int32_t m = s.mat[i];
+		memcpy(o + 31, &m, 4);
+	}
+}
+
+void emu_scene_get_materials(void* h, drt_material* out)
+{
+	const HostScene& s = ((EmuScene*)h)->host;
+	memcpy(out, s.materials.data(), s.materials.size() * sizeof(drt_material));
+}
+
+void emu_scene_get_texture_info(void* h, int i, int* w, int* hh, int* c)
+{
+	const HostTexture& t = ((EmuScene*)h)->host.textures[i];
+	*w = t.width; *hh = t.height; *c = t.comps;
+}
+void emu_scene_get_texture_pixels(void* h, int i, uint8_t* out)
+{
+	const HostTexture& t = ((EmuScene*)h)->host.textures[i];
+	memcpy(out, t.pixels.data(), t.pixels.size());
+}
+void emu_scene_get_wide_nodes(void* h, void* out) { EmuScene* s = (EmuScene*)h; memcpy(out, s->wide.data(), (size_t)s->result.wide_nodes * sizeof(WideNode)); }
+void emu_scene_get_leaf_triangles(void* h, void* out) { EmuScene* s = (EmuScene*)h; memcpy(out, s->out_tris.data(), (size_t)s->host.tri_count() * 48); }
+
+static RenderParams make_params(EmuScene* s, const drt_camera* cam, const drt_settings* st, int W, int H)
+{
+	RenderParams P;
+	memset(&P, 0, sizeof(P));
+	P.scene = s->view;
+	P.cam = make_camera_params(*cam, (uint32_t)W, (uint32_t)H);
+	drt_settings dflt;
+	if (!st) { default_settings(&dflt); st = &dflt; }
+	P.shade = make_shade_params(*st);
+	P.width = W; P.height = H;
+	return P;
+}
+
+// stats[0..5] = node visits, tri tests, ties, alpha tests, max stack, texel clamps
+void emu_trace_primary(void* h, const drt_camera* cam, int W, int H, unsigned frameidx, int strict, int rtl,
+	drt_hit* out, float* ray_od6, unsigned long long* stats)
+{
+	EmuScene* s = (EmuScene*)h;
+	RenderParams P = make_params(s, cam, nullptr, W, H);
+	unsigned long long tot[6] = { 0, 0, 0, 0, 0, 0 };
+#pragma omp parallel for schedule(dynamic, 8)
+	for (int y = 0; y < H; y++) {
+		TraceStats ts;
+		memset(&ts, 0, sizeof(ts));
+		for (int x = 0; x < W; x++) {
+			uint32_t seed = (uint32_t)x + (uint32_t)y * (uint32_t)W;
+			seed *= frameidx;
+			RayOD r = strict ? camera_get_ray<true>(P.cam, x, y, W, H, seed, rtl != 0) : camera_get_ray<false>(P.cam, x, y, W, H, seed, rtl != 0);
+			Hit hit;
+			if (strict) trace_ray<true, false, true>(P.scene, r.o, r.d, FLT_MAX, hit, &ts);
+			else trace_ray<false, false, true>(P.scene, r.o, r.d, FLT_MAX, hit, &ts);
+			size_t p = (size_t)x + (size_t)y * W;
+			out[p].prim_id = hit.prim >= 0 ? (int32_t)as_uint(P.scene.tris[3 * (size_t)hit.prim].w) : -1;
+			out[p].t = hit.prim >= 0 ? hit.t : -1.f; out[p].u = hit.u; out[p].v = hit.v;
+			if (ray_od6) { float* o = ray_od6 + 6 * p; o[0] = r.o.x; o[1] = r.o.y; o[2] = r.o.z; o[3] = r.d.x; o[4] = r.d.y; o[5] = r.d.z; }
+		}
+#pragma omp critical
+		{
+			tot[0] += ts.nodes; tot[1] += ts.tris; tot[2] += ts.ties; tot[3] += ts.alpha; tot[5] += ts.clamps;
+			if (ts.max_stack > tot[4]) tot[4] = ts.max_stack;
+		}
+	}
+	if (stats) memcpy(stats, tot, sizeof(tot));
+}
+
+// Accumulates frames first, first+stride, ... (n of them) into acc (W*H*3 floats), sequentially per pixel.
+// counters[0..7] = closest rays, shadow rays, node visits, tri tests, ties, alpha tests, max stack, clamps
+void emu_render(void* h, const drt_camera* cam, const drt_settings* st, int W, int H, unsigned first, unsigned stride,
+	unsigned n, int strict, int rtl, float* acc, unsigned long long* counters)
+{
+	EmuScene* s = (EmuScene*)h;
+	RenderParams P = make_params(s, cam, st, W, H);
+	unsigned long long tot[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+#pragma omp parallel for schedule(dynamic, 4)
+	for (int y = 0; y < H; y++) {
+		TraceStats ts;
+		memset(&ts, 0, sizeof(ts));
+		PathCounters pc;
+		pc.closest = pc.shadow = 0;
+		unsigned long long c0 = 0, c1 = 0;
+		for (int x = 0; x < W; x++) {
+			float* a = acc + 3 * ((size_t)x + (size_t)y * W);
+			for (unsigned k = 0; k < n; k++) {
+				unsigned f = first + k * stride;
+				V3 c = strict ? path_radiance<true, true>(P, x, y, f, rtl != 0, pc, &ts) : path_radiance<false, true>(P, x, y, f, rtl != 0, pc, &ts);
+				a[0] += c.x; a[1] += c.y; a[2] += c.z;
+			}
+			c0 += pc.closest; c1 += pc.shadow; pc.closest = pc.shadow = 0;
+		}
+#pragma omp critical
+		{
+			tot[0] += c0; tot[1] += c1; tot[2] += ts.nodes; tot[3] += ts.tris; tot[4] += ts.ties; tot[5] += ts.alpha; tot[7] += ts.clamps;
+			if (ts.max_stack > tot[6]) tot[6] = ts.max_stack;
+		}
+	}
+	if (counters) memcpy(counters, tot, sizeof(tot));
+}
+
+void emu_camera_params(const drt_camera* cam, int W, int H, float* out20)
+{
+	CameraParams c = make_camera_params(*cam, W, H);
+	memcpy(out20, &c, sizeof(float) * 20);
+}
+
+void emu_default_camera(drt_camera* c) { default_camera(c); }
+void emu_default_settings(drt_settings* s) { default_settings(s); }
+
+} // extern "C"
