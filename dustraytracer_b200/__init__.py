@@ -1,0 +1,11 @@
+"""dustraytracer_b200 -- B200-native path-tracing hot path behind the DustRayTracer library surface.
+
+    from dustraytracer_b200 import Scene, BVHBuilder, Renderer, Camera, RendererSettings
+
+The package is a thin host-side mirror (api.py) over libdrt.so (csrc/, C ABI in include/drt.h).
+"""
+from .api import (DRT_ACCUM_RGB32F, DRT_FLAG_HOST_ARG_ORDER, DRT_FLAG_STATS, DRT_FLAG_STRICT, DRT_RGBA8, DRT_RGBA32F,
+                  BVHBuilder, Camera, DrtError, Renderer, RendererSettings, Scene)
+
+__all__ = ["Scene", "BVHBuilder", "Renderer", "Camera", "RendererSettings", "DrtError",
+           "DRT_RGBA32F", "DRT_RGBA8", "DRT_ACCUM_RGB32F", "DRT_FLAG_STRICT", "DRT_FLAG_HOST_ARG_ORDER", "DRT_FLAG_STATS"]

@@ -1,0 +1,657 @@
+// drt_api.cu -- implementation of the C ABI declared in include/drt.h.
+//
+// Scene side : replaces Scene::loadGLTFmodel (Scene.cu:181-317) + BVHBuilder::build* (BVHBuilder.cu:11-145):
+//              host triangle soup -> HBM upload -> GPU binned-SAH build -> compressed wide nodes.
+// Render side: replaces Renderer::{ResizeBuffer,Render,resetAccumulationBuffer} (Renderer.cu:29-136) and
+//              InvokeRenderKernel (RenderKernel.cu:37-58); the GL texture / surface is a device float4 buffer.
+// No CPU fallback: every device operation reports DRT_ERR_CUDA when there is no usable GPU.
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "drt_host.h"
+#include "drt_kernels.h"
+#include "drt_params.h"
+
+namespace drt {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+
+static int fail(int code, const std::string& msg)
+{
+	set_error(msg);
+	return code;
+}
+
+#define DRT_CUDA(expr)                                                                                      \
+	do {                                                                                                    \
+		cudaError_t e__ = (expr);                                                                           \
+		if (e__ != cudaSuccess) {                                                                           \
+			cudaGetLastError();                                                                             \
+			return fail(DRT_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));                \
+		}                                                                                                   \
+	} while (0)
+
+template <class T> struct DevBuf {
+	T* p = nullptr;
+	size_t n = 0;
+	cudaError_t alloc(size_t count)
+	{
+		release();
+		n = count;
+		if (!count) return cudaSuccess;
+		return cudaMalloc((void**)&p, count * sizeof(T));
+	}
+	void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+	size_t bytes() const { return n * sizeof(T); }
+	~DevBuf() { release(); }
+};
+
+struct CudaExec : BuildExec {
+	cudaStream_t stream = nullptr;
+	cudaError_t last = cudaSuccess;
+	int launches = 0;
+	int check(cudaError_t e) { if (e != cudaSuccess) { last = e; return -1; } return 0; }
+	int launch(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n) override
+	{
+		launches++;
+		return check(launch_build_pass(pass, A, idx_final, a, b, n, stream));
+	}
+	int read_state(const BuildArrays& A, BuildState& out) override
+	{
+		if (check(cudaMemcpyAsync(&out, A.state, sizeof(BuildState), cudaMemcpyDeviceToHost, stream))) return -1;
+		return check(cudaStreamSynchronize(stream));
+	}
+	int write_state(const BuildArrays& A, const BuildState& in) override
+	{
+		return check(cudaMemcpyAsync(A.state, &in, sizeof(BuildState), cudaMemcpyHostToDevice, stream));
+	}
+	int write_root(const BuildArrays& A, const BuildNode& root, const BuildSplit& split) override
+	{
+		const int zero = 0;
+		if (check(cudaMemcpyAsync(A.nodes, &root, sizeof(root), cudaMemcpyHostToDevice, stream))) return -1;
+		if (check(cudaMemcpyAsync(A.splits, &split, sizeof(split), cudaMemcpyHostToDevice, stream))) return -1;
+		if (check(cudaMemcpyAsync(A.wide_src, &zero, sizeof(int), cudaMemcpyHostToDevice, stream))) return -1;
+		return check(cudaStreamSynchronize(stream)); // sources are stack variables
+	}
+};
+
+} // namespace drt
+
+using namespace drt;
+
+struct drt_scene {
+	HostScene host;
+	int device = -1;
+	bool built = false;
+	DevBuf<WideNode> nodes;
+	DevBuf<drt_f4> tris, shade, materials;
+	DevBuf<TexDesc> texdesc;
+	DevBuf<uint32_t> texels;
+	SceneView view;
+	drt_scene_stats stats;
+	drt_scene() { memset(&view, 0, sizeof(view)); memset(&stats, 0, sizeof(stats)); }
+};
+
+struct drt_renderer {
+	int device = 0;
+	cudaStream_t own_stream = nullptr;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	uint32_t width = 0, height = 0;
+	DevBuf<drt_f4> accum, display;
+	DevBuf<Counters> counters;
+	DevBuf<Hit> hits;
+	DevBuf<uint8_t> staging;
+	uint32_t frame_index = 1;   // the reference's m_FrameIndex (Renderer.hpp:41): next frame to render
+	uint32_t samples_done = 0;  // samples accumulated by THIS renderer
+	uint32_t first_frame = 1, stride = 1;
+	uint32_t flags = 0;
+	int variant = 0, block_threads = 0;
+	int kernel_launches = 0;
+};
+
+static void fill_stats(drt_scene* s)
+{
+	s->stats.triangles = s->host.tri_count();
+	s->stats.materials = s->host.materials.size();
+	s->stats.textures = s->host.textures.size();
+	s->stats.meshes = s->host.meshes;
+}
+
+extern "C" {
+
+const char* drt_last_error(void) { return g_last_error.c_str(); }
+const char* drt_version(void) { return "dustraytracer_b200 0.1 (sm_100a)"; }
+void drt_default_camera(drt_camera* out) { if (out) default_camera(out); }
+void drt_default_settings(drt_settings* out) { if (out) default_settings(out); }
+
+int drt_scene_load_gltf(const char* path, drt_scene** out)
+{
+	if (!path || !out) return fail(DRT_ERR_INVALID, "drt_scene_load_gltf: null argument");
+	*out = nullptr;
+	auto t0 = std::chrono::steady_clock::now();
+	drt_scene* s = new drt_scene();
+	std::string err;
+	int rc = load_gltf(path, s->host, err);
+	if (rc != DRT_OK) { delete s; return fail(rc, err); }
+	fill_stats(s);
+	s->stats.load_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+	*out = s;
+	return DRT_OK;
+}
+
+int drt_scene_from_triangles(const float* pos, const float* uv, const int32_t* material_index, size_t n_tris,
+	const drt_material* materials, size_t n_materials, drt_scene** out)
+{
+	if (!out || (n_tris && !pos) || (n_materials && !materials)) return fail(DRT_ERR_INVALID, "drt_scene_from_triangles: null argument");
+	if (n_tris > 0x7fffffffu / 3) return fail(DRT_ERR_INVALID, "drt_scene_from_triangles: too many triangles");
+	drt_scene* s = new drt_scene();
+	HostScene& h = s->host;
+	h.pos.assign(pos, pos + 9 * n_tris);
+	if (uv) h.uv.assign(uv, uv + 6 * n_tris); else h.uv.assign(6 * n_tris, 0.f);
+	h.vnormal.assign(9 * n_tris, 0.f);
+	h.fnormal.resize(3 * n_tris);
+	h.mat.resize(n_tris);
+	const float zero9[9] = { 0, 0, 0, 0, 0, 0, 0, 0, 0 };
+	for (size_t i = 0; i < n_tris; i++) {
+		compute_face_normal(pos + 9 * i, zero9, h.fnormal.data() + 3 * i);
+		h.mat[i] = material_index ? material_index[i] : 0;
+	}
+	h.materials.assign(materials, materials + n_materials);
+	h.meshes = 1;
+	fill_stats(s);
+	*out = s;
+	return DRT_OK;
+}
+
+int drt_scene_add_texture(drt_scene* scene, int32_t width, int32_t height, int32_t comps, const uint8_t* pixels)
+{
+	if (!scene || !pixels || width <= 0 || height <= 0 || comps < 1 || comps > 4) return fail(DRT_ERR_INVALID, "drt_scene_add_texture: bad argument");
+	HostTexture t;
+	t.width = width; t.height = height; t.comps = comps;
+	t.pixels.assign(pixels, pixels + (size_t)width * height * comps);
+	scene->host.textures.push_back(std::move(t));
+	scene->built = false;
+	fill_stats(scene);
+	return DRT_OK;
+}
+
+void drt_scene_destroy(drt_scene* scene)
+{
+	if (!scene) return;
+	if (scene->device >= 0) cudaSetDevice(scene->device);
+	delete scene;
+}
+
+int drt_scene_get_stats(const drt_scene* scene, drt_scene_stats* out)
+{
+	if (!scene || !out) return fail(DRT_ERR_INVALID, "drt_scene_get_stats: null argument");
+	*out = scene->stats;
+	return DRT_OK;
+}
+
+int drt_scene_get_triangles(const drt_scene* scene, void* out, size_t bytes)
+{
+	if (!scene || !out) return fail(DRT_ERR_INVALID, "drt_scene_get_triangles: null argument");
+	const HostScene& s = scene->host;
+	if (bytes < s.tri_count() * 128) return fail(DRT_ERR_INVALID, "drt_scene_get_triangles: buffer too small");
+	float* o = (float*)out;
+	for (size_t i = 0; i < s.tri_count(); i++, o += 32) {
+		const float* p = &s.pos[9 * i]; const float* n = &s.vnormal[9 * i]; const float* t = &s.uv[6 * i];
+		// centroid = (v0 + v1 + v2) / 3 (Triangle.cuh:11); 4 bytes of padding follow (float2 alignment)
+		o[0] = (p[0] + p[3] + p[6]) / 3; o[1] = (p[1] + p[4] + p[7]) / 3; o[2] = (p[2] + p[5] + p[8]) / 3; o[3] = 0.f;
+		for (int k = 0; k < 3; k++) {
+			float* v = o + 4 + 8 * k;
+			v[0] = p[3 * k]; v[1] = p[3 * k + 1]; v[2] = p[3 * k + 2];
+			v[3] = n[3 * k]; v[4] = n[3 * k + 1]; v[5] = n[3 * k + 2];
+			v[6] = t[2 * k]; v[7] = t[2 * k + 1];
+		}
+		o[28] = s.fnormal[3 * i]; o[29] = s.fnormal[3 * i + 1]; o[30] = s.fnormal[3 * i + 2];
+		memcpy(o + 31, &s.mat[i], 4);
+	}
+	return DRT_OK;
+}
+
+int drt_scene_get_materials(const drt_scene* scene, drt_material* out, size_t count)
+{
+	if (!scene || (!out && count)) return fail(DRT_ERR_INVALID, "drt_scene_get_materials: null argument");
+	if (count < scene->host.materials.size()) return fail(DRT_ERR_INVALID, "drt_scene_get_materials: buffer too small");
+	memcpy(out, scene->host.materials.data(), scene->host.materials.size() * sizeof(drt_material));
+	return DRT_OK;
+}
+
+int drt_scene_get_texture(const drt_scene* scene, int32_t index, int32_t* width, int32_t* height, int32_t* comps,
+	uint8_t* pixels_or_null, size_t bytes)
+{
+	if (!scene || index < 0 || (size_t)index >= scene->host.textures.size()) return fail(DRT_ERR_INVALID, "drt_scene_get_texture: bad index");
+	const HostTexture& t = scene->host.textures[index];
+	if (width) *width = t.width;
+	if (height) *height = t.height;
+	if (comps) *comps = t.comps;
+	if (pixels_or_null) {
+		if (bytes < t.pixels.size()) return fail(DRT_ERR_INVALID, "drt_scene_get_texture: buffer too small");
+		memcpy(pixels_or_null, t.pixels.data(), t.pixels.size());
+	}
+	return DRT_OK;
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// scene upload + GPU build
+// ---------------------------------------------------------------------------------------------
+extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* /*params_or_null*/, int device)
+{
+	if (!scene) return fail(DRT_ERR_INVALID, "drt_scene_build_bvh: null scene");
+	int ndev = 0;
+	DRT_CUDA(cudaGetDeviceCount(&ndev));
+	if (device < 0 || device >= ndev) return fail(DRT_ERR_CUDA, "drt_scene_build_bvh: no such CUDA device (this library has no CPU path)");
+	DRT_CUDA(cudaSetDevice(device));
+	scene->device = device;
+	scene->built = false;
+	const HostScene& h = scene->host;
+	const size_t n = h.tri_count();
+	if (n > 0x7fffffffu / 3) return fail(DRT_ERR_INVALID, "too many triangles");
+
+	cudaStream_t stream;
+	DRT_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+	struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamDestroy(s); } } guard{ stream };
+
+	// ---- tables: textures (RGBA8 pool), materials, per-triangle material word ----
+	std::vector<TexDesc> texdesc;
+	std::vector<uint32_t> texels;
+	for (const HostTexture& t : h.textures) {
+		TexDesc d;
+		d.offset = (uint32_t)texels.size(); d.width = t.width; d.height = t.height; d.comps = t.comps;
+		const size_t np = (size_t)t.width * t.height;
+		texels.reserve(texels.size() + np);
+		for (size_t p = 0; p < np; p++) {
+			const uint8_t* px = t.pixels.data() + p * t.comps;
+			uint32_t r = px[0], g = t.comps >= 3 ? px[1] : px[0], b = t.comps >= 3 ? px[2] : px[0];
+			uint32_t a = t.comps == 4 ? px[3] : (t.comps == 2 ? px[1] : 255u);
+			texels.push_back(r | (g << 8) | (b << 16) | (a << 24));
+		}
+		texdesc.push_back(d);
+	}
+	const size_t nm = h.materials.size();
+	std::vector<drt_f4> mats(nm + 1);
+	for (size_t i = 0; i <= nm; i++) {
+		drt_f4 m;
+		if (i < nm) {
+			int tex = h.materials[i].albedo_texture_index;
+			if (tex >= (int)h.textures.size()) tex = -1; // the reference would index past m_Textures
+			m.x = h.materials[i].albedo[0]; m.y = h.materials[i].albedo[1]; m.z = h.materials[i].albedo[2];
+			m.w = as_float((uint32_t)tex);
+		}
+		else { m.x = m.y = m.z = 1.f; m.w = as_float((uint32_t)-1); } // stand-in for material index -1 / out of range
+		mats[i] = m;
+	}
+	std::vector<int32_t> mat_word(n);
+	for (size_t i = 0; i < n; i++) {
+		int mi = h.mat[i];
+		if (mi < 0 || (size_t)mi >= nm) mi = (int)nm;
+		uint32_t flag = 0;
+		if ((size_t)mi < nm) {
+			int tex = h.materials[mi].albedo_texture_index;
+			if (tex >= 0 && tex < (int)h.textures.size() && h.textures[tex].comps == 4) flag = 0x80000000u; // AnyHit.cuh:17
+		}
+		mat_word[i] = (int32_t)((uint32_t)mi | flag);
+	}
+	DRT_CUDA(scene->texdesc.alloc(texdesc.size() ? texdesc.size() : 1));
+	DRT_CUDA(scene->texels.alloc(texels.size() ? texels.size() : 1));
+	DRT_CUDA(scene->materials.alloc(mats.size()));
+	if (!texdesc.empty()) DRT_CUDA(cudaMemcpyAsync(scene->texdesc.p, texdesc.data(), texdesc.size() * sizeof(TexDesc), cudaMemcpyHostToDevice, stream));
+	if (!texels.empty()) DRT_CUDA(cudaMemcpyAsync(scene->texels.p, texels.data(), texels.size() * 4, cudaMemcpyHostToDevice, stream));
+	DRT_CUDA(cudaMemcpyAsync(scene->materials.p, mats.data(), mats.size() * sizeof(drt_f4), cudaMemcpyHostToDevice, stream));
+
+	// ---- build inputs + scratch ----
+	DevBuf<float> d_pos, d_uv, d_fn;
+	DevBuf<int32_t> d_mat;
+	DevBuf<drt_f4> tri_lo, tri_hi;
+	DevBuf<int> idx0, idx1, pn0, pn1, bins, wide_src;
+	DevBuf<BuildNode> bnodes;
+	DevBuf<BuildSplit> bsplits;
+	DevBuf<BuildState> bstate;
+	DevBuf<WideNode> wide_tmp;
+	BuildResult res;
+	double build_ms = 0.0;
+	if (n > 0) {
+		DRT_CUDA(d_pos.alloc(9 * n)); DRT_CUDA(d_uv.alloc(6 * n)); DRT_CUDA(d_fn.alloc(3 * n)); DRT_CUDA(d_mat.alloc(n));
+		DRT_CUDA(tri_lo.alloc(n)); DRT_CUDA(tri_hi.alloc(n));
+		DRT_CUDA(idx0.alloc(n)); DRT_CUDA(idx1.alloc(n)); DRT_CUDA(pn0.alloc(n)); DRT_CUDA(pn1.alloc(n));
+		DRT_CUDA(bnodes.alloc(2 * n + 2)); DRT_CUDA(bsplits.alloc(2 * n + 2)); DRT_CUDA(bstate.alloc(1));
+		DRT_CUDA(bins.alloc(build_bin_slots_capacity((int)n) * 3 * DRT_BINS * DRT_BIN_WORDS));
+		DRT_CUDA(wide_src.alloc(n + 1)); DRT_CUDA(wide_tmp.alloc(n + 1));
+		DRT_CUDA(scene->tris.alloc(3 * n)); DRT_CUDA(scene->shade.alloc(3 * n));
+		DRT_CUDA(cudaMemcpyAsync(d_pos.p, h.pos.data(), 9 * n * 4, cudaMemcpyHostToDevice, stream));
+		DRT_CUDA(cudaMemcpyAsync(d_uv.p, h.uv.data(), 6 * n * 4, cudaMemcpyHostToDevice, stream));
+		DRT_CUDA(cudaMemcpyAsync(d_fn.p, h.fnormal.data(), 3 * n * 4, cudaMemcpyHostToDevice, stream));
+		DRT_CUDA(cudaMemcpyAsync(d_mat.p, mat_word.data(), n * 4, cudaMemcpyHostToDevice, stream));
+		DRT_CUDA(cudaStreamSynchronize(stream));
+
+		BuildArrays A;
+		memset(&A, 0, sizeof(A));
+		A.pos = d_pos.p; A.uv = d_uv.p; A.fnormal = d_fn.p; A.mat = d_mat.p; A.n = (int)n;
+		A.tri_lo = tri_lo.p; A.tri_hi = tri_hi.p;
+		A.idx_in = idx0.p; A.idx_out = idx1.p; A.pnode_in = pn0.p; A.pnode_out = pn1.p;
+		A.nodes = bnodes.p; A.splits = bsplits.p; A.bins = bins.p; A.state = bstate.p;
+		A.wide_src = wide_src.p; A.wide = wide_tmp.p; A.out_tris = scene->tris.p; A.out_shade = scene->shade.p;
+		CudaExec ex;
+		ex.stream = stream;
+		cudaEvent_t e0, e1;
+		DRT_CUDA(cudaEventCreate(&e0)); DRT_CUDA(cudaEventCreate(&e1));
+		DRT_CUDA(cudaEventRecord(e0, stream));
+		int rc = run_build(ex, A, res);
+		cudaEventRecord(e1, stream);
+		cudaError_t se = cudaStreamSynchronize(stream);
+		float ms = 0.f;
+		cudaEventElapsedTime(&ms, e0, e1);
+		cudaEventDestroy(e0); cudaEventDestroy(e1);
+		if (rc != 0 || se != cudaSuccess) {
+			cudaGetLastError();
+			return fail(DRT_ERR_CUDA, std::string("BVH build failed: ") + cudaGetErrorString(ex.last != cudaSuccess ? ex.last : se));
+		}
+		build_ms = ms;
+		if (res.tris_emitted != (int)n) return fail(DRT_ERR_CUDA, "BVH build emitted " + std::to_string(res.tris_emitted) + " of " + std::to_string(n) + " triangles");
+		// keep only the wide nodes that exist
+		DRT_CUDA(scene->nodes.alloc((size_t)res.wide_nodes));
+		DRT_CUDA(cudaMemcpyAsync(scene->nodes.p, wide_tmp.p, (size_t)res.wide_nodes * sizeof(WideNode), cudaMemcpyDeviceToDevice, stream));
+		DRT_CUDA(cudaStreamSynchronize(stream));
+	}
+	else {
+		scene->nodes.release(); scene->tris.release(); scene->shade.release();
+		DRT_CUDA(cudaStreamSynchronize(stream));
+	}
+
+	SceneView& v = scene->view;
+	v.nodes = (const drt_u4*)scene->nodes.p;
+	v.tris = scene->tris.p; v.shade = scene->shade.p; v.materials = scene->materials.p;
+	v.textures = scene->texdesc.p; v.texels = scene->texels.p;
+	v.num_tris = (int32_t)n; v.num_nodes = res.wide_nodes; v.num_materials = (int32_t)mats.size(); v.num_textures = (int32_t)texdesc.size();
+	scene->stats.wide_nodes = (uint64_t)res.wide_nodes;
+	scene->stats.bvh2_nodes = (uint64_t)res.bvh2_nodes;
+	scene->stats.bvh_levels = (uint64_t)res.levels;
+	scene->stats.build_ms = build_ms;
+	scene->stats.device_bytes = scene->nodes.bytes() + scene->tris.bytes() + scene->shade.bytes() + scene->materials.bytes()
+		+ scene->texdesc.bytes() + scene->texels.bytes();
+	scene->built = true;
+	return DRT_OK;
+}
+
+extern "C" int drt_scene_get_wide_nodes(const drt_scene* scene, void* out, size_t bytes)
+{
+	if (!scene || !out || !scene->built) return fail(DRT_ERR_INVALID, "drt_scene_get_wide_nodes: scene not built");
+	if (bytes < scene->nodes.bytes()) return fail(DRT_ERR_INVALID, "drt_scene_get_wide_nodes: buffer too small");
+	DRT_CUDA(cudaSetDevice(scene->device));
+	if (scene->nodes.n) DRT_CUDA(cudaMemcpy(out, scene->nodes.p, scene->nodes.bytes(), cudaMemcpyDeviceToHost));
+	return DRT_OK;
+}
+
+extern "C" int drt_scene_get_leaf_triangles(const drt_scene* scene, void* out, size_t bytes)
+{
+	if (!scene || !out || !scene->built) return fail(DRT_ERR_INVALID, "drt_scene_get_leaf_triangles: scene not built");
+	if (bytes < scene->tris.bytes()) return fail(DRT_ERR_INVALID, "drt_scene_get_leaf_triangles: buffer too small");
+	DRT_CUDA(cudaSetDevice(scene->device));
+	if (scene->tris.n) DRT_CUDA(cudaMemcpy(out, scene->tris.p, scene->tris.bytes(), cudaMemcpyDeviceToHost));
+	return DRT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// renderer
+// ---------------------------------------------------------------------------------------------
+static int renderer_bind(drt_renderer* r)
+{
+	DRT_CUDA(cudaSetDevice(r->device));
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_create(int device, drt_renderer** out)
+{
+	if (!out) return fail(DRT_ERR_INVALID, "drt_renderer_create: null argument");
+	*out = nullptr;
+	int ndev = 0;
+	DRT_CUDA(cudaGetDeviceCount(&ndev));
+	if (device < 0 || device >= ndev) return fail(DRT_ERR_CUDA, "drt_renderer_create: no such CUDA device (this library has no CPU path)");
+	DRT_CUDA(cudaSetDevice(device));
+	drt_renderer* r = new drt_renderer();
+	r->device = device;
+	cudaError_t e = cudaStreamCreateWithFlags(&r->own_stream, cudaStreamNonBlocking);
+	if (e == cudaSuccess) e = cudaEventCreate(&r->ev0);
+	if (e == cudaSuccess) e = cudaEventCreate(&r->ev1);
+	if (e == cudaSuccess) e = r->counters.alloc(1);
+	if (e == cudaSuccess) e = cudaMemset(r->counters.p, 0, sizeof(Counters));
+	if (e != cudaSuccess) { delete r; return fail(DRT_ERR_CUDA, std::string("drt_renderer_create: ") + cudaGetErrorString(e)); }
+	r->stream = r->own_stream;
+	*out = r;
+	return DRT_OK;
+}
+
+extern "C" void drt_renderer_destroy(drt_renderer* r)
+{
+	if (!r) return;
+	cudaSetDevice(r->device);
+	cudaStreamSynchronize(r->stream);
+	if (r->ev0) cudaEventDestroy(r->ev0);
+	if (r->ev1) cudaEventDestroy(r->ev1);
+	if (r->own_stream) cudaStreamDestroy(r->own_stream);
+	delete r;
+}
+
+extern "C" int drt_renderer_set_stream(drt_renderer* r, void* cuda_stream)
+{
+	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_set_stream: null renderer");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	r->stream = cuda_stream ? (cudaStream_t)cuda_stream : r->own_stream;
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_set_flags(drt_renderer* r, uint32_t flags)
+{
+	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_set_flags: null renderer");
+	r->flags = flags;
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads)
+{
+	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: null renderer");
+	if (variant < 0 || variant > 1 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
+	r->variant = variant; r->block_threads = block_threads;
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_set_frame_schedule(drt_renderer* r, uint32_t first_frame, uint32_t stride)
+{
+	if (!r || first_frame == 0 || stride == 0) return fail(DRT_ERR_INVALID, "drt_renderer_set_frame_schedule: first_frame and stride must be >= 1");
+	r->first_frame = first_frame; r->stride = stride;
+	return drt_renderer_reset(r);
+}
+
+extern "C" int drt_renderer_reset(drt_renderer* r)
+{
+	// resetAccumulationBuffer (Renderer.cu:132-136): zero the sums, frame index back to 1
+	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_reset: null renderer");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	if (r->accum.n) DRT_CUDA(cudaMemsetAsync(r->accum.p, 0, r->accum.bytes(), r->stream));
+	if (r->display.n) DRT_CUDA(cudaMemsetAsync(r->display.p, 0, r->display.bytes(), r->stream));
+	r->frame_index = 1;
+	r->samples_done = 0;
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_resize(drt_renderer* r, uint32_t width, uint32_t height)
+{
+	// ResizeBuffer (Renderer.cu:29-78): no-op when unchanged, otherwise reallocate and reset
+	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_resize: null renderer");
+	if (width == 0 || height == 0 || (uint64_t)width * height > 0x7fffffffull) return fail(DRT_ERR_INVALID, "drt_renderer_resize: bad size");
+	if (width == r->width && height == r->height) return DRT_OK;
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	const size_t n = (size_t)width * height;
+	DRT_CUDA(r->accum.alloc(n));
+	DRT_CUDA(r->display.alloc(n));
+	r->hits.release(); r->staging.release();
+	r->width = width; r->height = height;
+	return drt_renderer_reset(r);
+}
+
+extern "C" uint32_t drt_renderer_sample_count(const drt_renderer* r) { return r ? r->frame_index : 0; }
+extern "C" uint32_t drt_renderer_width(const drt_renderer* r) { return r ? r->width : 0; }
+extern "C" uint32_t drt_renderer_height(const drt_renderer* r) { return r ? r->height : 0; }
+extern "C" int drt_renderer_kernel_launches(const drt_renderer* r) { return r ? r->kernel_launches : 0; }
+
+static int make_render_params(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, const drt_settings* settings, RenderParams& P)
+{
+	if (!r || !cam || !scene) return fail(DRT_ERR_INVALID, "render: null argument");
+	if (!scene->built) return fail(DRT_ERR_INVALID, "render: call drt_scene_build_bvh first");
+	if (scene->device != r->device) return fail(DRT_ERR_INVALID, "render: scene was built on another device");
+	if (!r->width) return fail(DRT_ERR_INVALID, "render: call drt_renderer_resize first");
+	memset(&P, 0, sizeof(P));
+	P.scene = scene->view;
+	P.cam = make_camera_params(*cam, r->width, r->height);
+	drt_settings dflt;
+	if (!settings) { default_settings(&dflt); settings = &dflt; }
+	P.shade = make_shade_params(*settings);
+	P.width = (int32_t)r->width; P.height = (int32_t)r->height;
+	P.accum = r->accum.p; P.display = r->display.p; P.counters = r->counters.p;
+	return DRT_OK;
+}
+
+static LaunchConfig launch_config(const drt_renderer* r)
+{
+	LaunchConfig cfg;
+	cfg.strict = (r->flags & DRT_FLAG_STRICT) != 0;
+	cfg.rtl = (r->flags & DRT_FLAG_HOST_ARG_ORDER) != 0;
+	cfg.stats = (r->flags & DRT_FLAG_STATS) != 0;
+	cfg.variant = r->variant; cfg.block_threads = r->block_threads;
+	return cfg;
+}
+
+extern "C" int drt_renderer_render(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, const drt_settings* settings,
+	uint32_t n_samples, float* ms_or_null)
+{
+	if (ms_or_null) *ms_or_null = 0.f;
+	RenderParams P;
+	int rc = make_render_params(r, cam, scene, settings, P);
+	if (rc) return rc;
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	drt_settings dflt;
+	if (!settings) { default_settings(&dflt); settings = &dflt; }
+	// Renderer.cu:82: nothing is rendered once the frame index equals max_samples
+	const uint64_t next_frame = (uint64_t)r->first_frame + (uint64_t)r->samples_done * r->stride;
+	const int64_t max_samples = settings->max_samples;
+	uint32_t n = n_samples;
+	if ((int64_t)next_frame >= max_samples) {
+		if ((int64_t)next_frame == max_samples || r->stride > 1) n = 0; // the reference only tests equality
+	}
+	else {
+		const uint64_t room = ((uint64_t)max_samples - next_frame + r->stride - 1) / r->stride;
+		if (n > room) n = (uint32_t)room;
+	}
+	if (n == 0) return DRT_OK;
+	P.frame_first = (uint32_t)next_frame;
+	P.frame_stride = r->stride;
+	P.n_samples = n;
+	P.total_samples = (float)(r->samples_done + n); // = the frame index the reference divides by (RenderKernel.cu:30)
+	DRT_CUDA(cudaEventRecord(r->ev0, r->stream));
+	DRT_CUDA(launch_render(P, launch_config(r), r->stream, &r->kernel_launches));
+	DRT_CUDA(cudaEventRecord(r->ev1, r->stream));
+	DRT_CUDA(cudaEventSynchronize(r->ev1)); // like Renderer.cu:105-106 the call returns with the frame done
+	if (ms_or_null) DRT_CUDA(cudaEventElapsedTime(ms_or_null, r->ev0, r->ev1));
+	r->samples_done += n;
+	r->frame_index += n;
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_resolve(drt_renderer* r, uint32_t total_samples)
+{
+	if (!r || !r->width || total_samples == 0) return fail(DRT_ERR_INVALID, "drt_renderer_resolve: bad argument");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	DRT_CUDA(launch_resolve(r->display.p, r->accum.p, (int)((size_t)r->width * r->height), (float)total_samples, r->stream));
+	r->kernel_launches++;
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_accum_device_ptr(drt_renderer* r, void** ptr, size_t* bytes)
+{
+	if (!r || !ptr || !r->width) return fail(DRT_ERR_INVALID, "drt_renderer_accum_device_ptr: renderer has no buffer");
+	*ptr = r->accum.p;
+	if (bytes) *bytes = r->accum.bytes();
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_readback(drt_renderer* r, drt_format format, void* host, size_t bytes)
+{
+	if (!r || !host || !r->width) return fail(DRT_ERR_INVALID, "drt_renderer_readback: bad argument");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	const size_t n = (size_t)r->width * r->height;
+	if (format == DRT_RGBA32F) {
+		if (bytes < n * 16) return fail(DRT_ERR_INVALID, "drt_renderer_readback: buffer too small");
+		DRT_CUDA(cudaMemcpyAsync(host, r->display.p, n * 16, cudaMemcpyDeviceToHost, r->stream));
+	}
+	else if (format == DRT_RGBA8 || format == DRT_ACCUM_RGB32F) {
+		const size_t need = format == DRT_RGBA8 ? n * 4 : n * 12;
+		if (bytes < need) return fail(DRT_ERR_INVALID, "drt_renderer_readback: buffer too small");
+		if (r->staging.n < need) DRT_CUDA(r->staging.alloc(need));
+		if (format == DRT_RGBA8) DRT_CUDA(launch_pack_rgba8((uint32_t*)r->staging.p, r->display.p, (int)n, r->stream));
+		else DRT_CUDA(launch_pack_rgb32f((float*)r->staging.p, r->accum.p, (int)n, r->stream));
+		r->kernel_launches++;
+		DRT_CUDA(cudaMemcpyAsync(host, r->staging.p, need, cudaMemcpyDeviceToHost, r->stream));
+	}
+	else return fail(DRT_ERR_INVALID, "drt_renderer_readback: unknown format");
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_upload_accum(drt_renderer* r, const float* rgb32f, size_t bytes, uint32_t samples_done)
+{
+	// checkpoint / resume of a progressive render: restores sums + sample count
+	if (!r || !rgb32f || !r->width) return fail(DRT_ERR_INVALID, "drt_renderer_upload_accum: bad argument");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	const size_t n = (size_t)r->width * r->height;
+	if (bytes < n * 12) return fail(DRT_ERR_INVALID, "drt_renderer_upload_accum: buffer too small");
+	std::vector<drt_f4> tmp(n);
+	for (size_t i = 0; i < n; i++) { tmp[i].x = rgb32f[3 * i]; tmp[i].y = rgb32f[3 * i + 1]; tmp[i].z = rgb32f[3 * i + 2]; tmp[i].w = 0.f; }
+	DRT_CUDA(cudaMemcpyAsync(r->accum.p, tmp.data(), n * 16, cudaMemcpyHostToDevice, r->stream));
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	r->samples_done = samples_done;
+	r->frame_index = samples_done + 1;
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_get_counters(drt_renderer* r, drt_counters* out, int reset)
+{
+	if (!r || !out) return fail(DRT_ERR_INVALID, "drt_renderer_get_counters: null argument");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	static_assert(sizeof(Counters) == sizeof(drt_counters), "counter layouts must match");
+	DRT_CUDA(cudaMemcpyAsync(out, r->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, r->stream));
+	if (reset) DRT_CUDA(cudaMemsetAsync(r->counters.p, 0, sizeof(Counters), r->stream));
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	return DRT_OK;
+}
+
+extern "C" int drt_trace_primary(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, uint32_t frame_index,
+	drt_hit* out_host, size_t count)
+{
+	RenderParams P;
+	int rc = make_render_params(r, cam, scene, nullptr, P);
+	if (rc) return rc;
+	if (!out_host) return fail(DRT_ERR_INVALID, "drt_trace_primary: null output");
+	const size_t n = (size_t)r->width * r->height;
+	if (count < n) return fail(DRT_ERR_INVALID, "drt_trace_primary: output too small");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	if (r->hits.n < n) DRT_CUDA(r->hits.alloc(n));
+	static_assert(sizeof(Hit) == sizeof(drt_hit), "hit layouts must match");
+	DRT_CUDA(launch_trace_primary(P, frame_index, r->hits.p, launch_config(r), r->stream));
+	r->kernel_launches++;
+	DRT_CUDA(cudaMemcpyAsync(out_host, r->hits.p, n * sizeof(Hit), cudaMemcpyDeviceToHost, r->stream));
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	return DRT_OK;
+}

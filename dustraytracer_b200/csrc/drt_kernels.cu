@@ -1,0 +1,222 @@
+// drt_kernels.cu -- sm_100a kernels of the hot path and of the GPU BVH builder.
+//
+// Render kernels (replace the reference's single `kernel`, DustRayTracer/src/Core/Kernel/RenderKernel.cu:20-35,
+// launched once per sample with 8x8 blocks, Renderer.hpp:43-44):
+//   variant 0  k_render_flat   one thread per pixel, ALL samples of the launch in one flat state machine
+//                              with a single traversal call site (drt_shade.cuh render_pixel_flat):
+//                              accumulator lives in registers, one 16-byte accum read + write and one
+//                              16-byte display write per pixel per LAUNCH instead of 40 B per sample.
+//   variant 1  k_render_loop   one thread per pixel, sample loop around the reference-shaped bounce loop
+//                              (path_radiance); also serves the debug views.
+// Warps cover 8x4 pixel tiles (coherent primary rays); blocks are rows of such tiles.
+#include "drt_kernels.h"
+#include "drt_shade.cuh"
+
+namespace drt {
+
+namespace {
+
+__device__ __forceinline__ void pixel_of_thread(int width, int height, int warps_per_block, int& x, int& y, bool& valid)
+{
+	// 8x4 pixel tile per warp; tiles numbered row-major over the image
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int tiles_x = (width + 7) >> 3;
+	const long long tile = (long long)blockIdx.x * warps_per_block + warp;
+	const int ty = (int)(tile / tiles_x), tx = (int)(tile - (long long)ty * tiles_x);
+	x = tx * 8 + (lane & 7);
+	y = ty * 4 + (lane >> 3);
+	valid = x < width && y < height;
+}
+
+__device__ __forceinline__ void flush_counters(Counters* c, const PathCounters& pc, const TraceStats* st)
+{
+	unsigned closest = __reduce_add_sync(0xffffffffu, pc.closest);
+	unsigned shadow = __reduce_add_sync(0xffffffffu, pc.shadow);
+	if ((threadIdx.x & 31) == 0) {
+		atomicAdd(&c->closest_rays, (unsigned long long)closest);
+		atomicAdd(&c->shadow_rays, (unsigned long long)shadow);
+	}
+	if (st) {
+		unsigned n = __reduce_add_sync(0xffffffffu, st->nodes), t = __reduce_add_sync(0xffffffffu, st->tris);
+		unsigned ti = __reduce_add_sync(0xffffffffu, st->ties), a = __reduce_add_sync(0xffffffffu, st->alpha);
+		unsigned cl = __reduce_add_sync(0xffffffffu, st->clamps), ms = __reduce_max_sync(0xffffffffu, st->max_stack);
+		if ((threadIdx.x & 31) == 0) {
+			atomicAdd(&c->node_visits, (unsigned long long)n);
+			atomicAdd(&c->tri_tests, (unsigned long long)t);
+			atomicAdd(&c->tie_events, (unsigned long long)ti);
+			atomicAdd(&c->alpha_tests, (unsigned long long)a);
+			atomicAdd(&c->texel_clamps, (unsigned long long)cl);
+			atomicMax(&c->max_stack, (unsigned long long)ms);
+		}
+	}
+}
+
+template <bool STRICT, bool STATS, int VARIANT>
+__global__ void __launch_bounds__(256) k_render(const __grid_constant__ RenderParams P, const bool rtl, const int warps_per_block)
+{
+	int x, y;
+	bool valid;
+	pixel_of_thread(P.width, P.height, warps_per_block, x, y, valid);
+	PathCounters pc;
+	pc.closest = 0; pc.shadow = 0;
+	TraceStats ts;
+	ts.nodes = ts.tris = ts.ties = ts.alpha = ts.max_stack = ts.clamps = 0;
+	TraceStats* st = STATS ? &ts : nullptr;
+	if (valid) {
+		const size_t p = (size_t)x + (size_t)y * (size_t)P.width;
+		const float4 a4 = P.accum[p];
+		V3 acc = mk3(a4.x, a4.y, a4.z);
+		if (VARIANT == 0 && P.shade.render_mode == DRT_RENDER_NORMAL) {
+			acc = render_pixel_flat<STRICT, STATS>(P, (uint32_t)x, (uint32_t)y, rtl, acc, pc, st);
+		}
+		else {
+			for (uint32_t k = 0; k < P.n_samples; k++) {
+				const uint32_t frameidx = P.frame_first + k * P.frame_stride;
+				const V3 c = path_radiance<STRICT, STATS>(P, (uint32_t)x, (uint32_t)y, frameidx, rtl, pc, st);
+				acc = M<STRICT>::add3(acc, c);
+			}
+		}
+		P.accum[p] = make_float4(acc.x, acc.y, acc.z, 0.f);
+		// display = acc / frameidx, alpha 1 (RenderKernel.cu:30-31)
+		P.display[p] = make_float4(acc.x / P.total_samples, acc.y / P.total_samples, acc.z / P.total_samples, 1.f);
+	}
+	flush_counters(P.counters, pc, st);
+}
+
+template <bool STRICT>
+__global__ void __launch_bounds__(256) k_trace_primary(const __grid_constant__ RenderParams P, const uint32_t frameidx, Hit* out,
+	const bool rtl, const int warps_per_block)
+{
+	int x, y;
+	bool valid;
+	pixel_of_thread(P.width, P.height, warps_per_block, x, y, valid);
+	TraceStats ts;
+	ts.nodes = ts.tris = ts.ties = ts.alpha = ts.max_stack = ts.clamps = 0;
+	PathCounters pc;
+	pc.closest = valid ? 1u : 0u; pc.shadow = 0;
+	if (valid) {
+		uint32_t seed = (uint32_t)x + (uint32_t)y * (uint32_t)P.width;
+		seed *= frameidx;
+		const RayOD r = camera_get_ray<STRICT>(P.cam, (uint32_t)x, (uint32_t)y, (uint32_t)P.width, (uint32_t)P.height, seed, rtl);
+		Hit hit;
+		trace_ray<STRICT, false, true>(P.scene, r.o, r.d, FLT_MAX, hit, &ts);
+		Hit o;
+		o.prim = hit.prim >= 0 ? (int32_t)as_uint(ld_f4(P.scene.tris + 3 * (size_t)hit.prim).w) : -1;
+		o.t = hit.prim >= 0 ? hit.t : -1.f;
+		o.u = hit.u; o.v = hit.v;
+		out[(size_t)x + (size_t)y * (size_t)P.width] = o;
+	}
+	flush_counters(P.counters, pc, &ts);
+}
+
+__global__ void k_resolve(float4* display, const float4* accum, int n, float total)
+{
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float4 a = accum[i];
+	display[i] = make_float4(a.x / total, a.y / total, a.z / total, 1.f);
+}
+
+__global__ void k_pack_rgba8(uint32_t* out, const float4* display, int n)
+{
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float4 c = display[i];
+	// what glGetTexImage(GL_RGBA, GL_UNSIGNED_BYTE) yields from the RGBA32F target (EditorLayer.cpp:85-97):
+	// clamp to [0,1], scale by 255, round to nearest
+	uint32_t r = (uint32_t)__float2int_rn(__saturatef(c.x) * 255.f), g = (uint32_t)__float2int_rn(__saturatef(c.y) * 255.f);
+	uint32_t b = (uint32_t)__float2int_rn(__saturatef(c.z) * 255.f), a = (uint32_t)__float2int_rn(__saturatef(c.w) * 255.f);
+	out[i] = r | (g << 8) | (b << 16) | (a << 24);
+}
+
+__global__ void k_pack_rgb32f(float* out, const float4* accum, int n)
+{
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float4 a = accum[i];
+	out[3 * (size_t)i] = a.x; out[3 * (size_t)i + 1] = a.y; out[3 * (size_t)i + 2] = a.z;
+}
+
+// ---- builder passes: one thread per element, bodies in drt_build.cuh ----
+template <int PASS>
+__global__ void __launch_bounds__(256) k_build(const BuildArrays A, const int* idx_final, int a, int b, int n)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	if (PASS == PASS_PRIM_BOUNDS) prim_bounds(A, i);
+	else if (PASS == PASS_INIT_BINS) init_bin_word(A, i, a);
+	else if (PASS == PASS_BIN) bin_prim(A, i);
+	else if (PASS == PASS_SPLIT) split_node(A, i);
+	else if (PASS == PASS_PARTITION) partition_prim(A, i);
+	else if (PASS == PASS_COLLAPSE) collapse_node(A, idx_final, a, b, i);
+}
+
+template <bool STRICT, bool STATS>
+cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s)
+{
+	const int threads = cfg.block_threads > 0 ? cfg.block_threads : 128;
+	const int wpb = threads / 32;
+	const long long tiles = (long long)((P.width + 7) / 8) * ((P.height + 3) / 4);
+	const unsigned blocks = (unsigned)((tiles + wpb - 1) / wpb);
+	if (cfg.variant == 1) k_render<STRICT, STATS, 1><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb);
+	else k_render<STRICT, STATS, 0><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb);
+	return cudaGetLastError();
+}
+
+} // namespace
+
+cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches)
+{
+	if (launches) *launches += 1;
+	if (cfg.block_threads % 32 != 0 || cfg.block_threads > 256) return cudaErrorInvalidValue;
+	if (cfg.strict) return cfg.stats ? launch_render_v<true, true>(P, cfg, s) : launch_render_v<true, false>(P, cfg, s);
+	return cfg.stats ? launch_render_v<false, true>(P, cfg, s) : launch_render_v<false, false>(P, cfg, s);
+}
+
+cudaError_t launch_trace_primary(const RenderParams& P, uint32_t frame_index, Hit* out_dev, const LaunchConfig& cfg, cudaStream_t s)
+{
+	const int threads = 128, wpb = threads / 32;
+	const long long tiles = (long long)((P.width + 7) / 8) * ((P.height + 3) / 4);
+	const unsigned blocks = (unsigned)((tiles + wpb - 1) / wpb);
+	if (cfg.strict) k_trace_primary<true><<<blocks, threads, 0, s>>>(P, frame_index, out_dev, cfg.rtl, wpb);
+	else k_trace_primary<false><<<blocks, threads, 0, s>>>(P, frame_index, out_dev, cfg.rtl, wpb);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_resolve(drt_f4* display, const drt_f4* accum, int n, float total, cudaStream_t s)
+{
+	if (n <= 0) return cudaSuccess;
+	k_resolve<<<(n + 255) / 256, 256, 0, s>>>(display, accum, n, total);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_pack_rgba8(uint32_t* out, const drt_f4* display, int n, cudaStream_t s)
+{
+	if (n <= 0) return cudaSuccess;
+	k_pack_rgba8<<<(n + 255) / 256, 256, 0, s>>>(out, display, n);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_pack_rgb32f(float* out, const drt_f4* accum, int n, cudaStream_t s)
+{
+	if (n <= 0) return cudaSuccess;
+	k_pack_rgb32f<<<(n + 255) / 256, 256, 0, s>>>(out, accum, n);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s)
+{
+	if (n <= 0) return cudaSuccess;
+	const unsigned blocks = (unsigned)((n + 255) / 256);
+	switch (pass) {
+	case PASS_PRIM_BOUNDS: k_build<PASS_PRIM_BOUNDS><<<blocks, 256, 0, s>>>(A, idx_final, a, b, n); break;
+	case PASS_INIT_BINS: k_build<PASS_INIT_BINS><<<blocks, 256, 0, s>>>(A, idx_final, a, b, n); break;
+	case PASS_BIN: k_build<PASS_BIN><<<blocks, 256, 0, s>>>(A, idx_final, a, b, n); break;
+	case PASS_SPLIT: k_build<PASS_SPLIT><<<blocks, 256, 0, s>>>(A, idx_final, a, b, n); break;
+	case PASS_PARTITION: k_build<PASS_PARTITION><<<blocks, 256, 0, s>>>(A, idx_final, a, b, n); break;
+	case PASS_COLLAPSE: k_build<PASS_COLLAPSE><<<blocks, 256, 0, s>>>(A, idx_final, a, b, n); break;
+	}
+	return cudaGetLastError();
+}
+
+} // namespace drt

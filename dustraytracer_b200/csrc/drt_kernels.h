@@ -1,0 +1,24 @@
+// drt_kernels.h -- launch entry points of drt_kernels.cu (host-callable, one CUDA stream each).
+#pragma once
+#include <cuda_runtime.h>
+#include "drt_types.h"
+#include "drt_build_driver.h"
+
+namespace drt {
+
+struct LaunchConfig {
+	bool strict = false;  // DRT_FLAG_STRICT
+	bool rtl = false;     // DRT_FLAG_HOST_ARG_ORDER
+	bool stats = false;   // DRT_FLAG_STATS
+	int variant = 0;      // render kernel variant (see drt_kernels.cu); 0 = default
+	int block_threads = 0; // 0 = variant default
+};
+
+cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s);
+cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches);
+cudaError_t launch_trace_primary(const RenderParams& P, uint32_t frame_index, Hit* out_dev, const LaunchConfig& cfg, cudaStream_t s);
+cudaError_t launch_resolve(drt_f4* display, const drt_f4* accum, int n_pixels, float total_samples, cudaStream_t s);
+cudaError_t launch_pack_rgba8(uint32_t* out, const drt_f4* display, int n_pixels, cudaStream_t s);
+cudaError_t launch_pack_rgb32f(float* out, const drt_f4* accum, int n_pixels, cudaStream_t s);
+
+} // namespace drt

@@ -149,4 +149,105 @@ DRT_HD V3 path_radiance(const RenderParams& P, uint32_t x, uint32_t y, uint32_t 
 	return light;
 }
 
+template <bool STRICT>
+DRT_HD V3 post_process(const RenderParams& P, V3 light)
+{
+	typedef M<STRICT> m;
+	const ShadeParams& S = P.shade;
+	if (S.render_mode == DRT_RENDER_NORMAL || S.debug_mode == DRT_DEBUG_ALBEDO) {
+		if (S.tone_mapping) {
+			V3 e = m::scale(light, P.cam.exposure);
+			light = m::scale(mk3(tonemap_partial<STRICT>(e.x), tonemap_partial<STRICT>(e.y), tonemap_partial<STRICT>(e.z)), S.white_scale);
+		}
+		if (S.gamma_correction) light = mk3(m::sqrt(light.x), m::sqrt(light.y), m::sqrt(light.z));
+	}
+	return light;
+}
+
+// All samples of one pixel as a flat state machine with ONE traversal call site: every loop trip
+// traces the lane's current ray -- a path segment (closest hit) or a sun shadow ray (any hit) -- then
+// advances that lane's path; a lane whose path ends starts its next sample at once instead of
+// waiting for the longest path of the warp. Per-lane results are identical to calling
+// path_radiance() once per sample (same RNG stream, same operation order, same accumulation order).
+// NORMALMODE only (debug views go through path_radiance).
+template <bool STRICT, bool STATS>
+DRT_HD V3 render_pixel_flat(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, V3 acc, PathCounters& pc, TraceStats* st)
+{
+	typedef M<STRICT> m;
+	const SceneView& sc = P.scene;
+	const ShadeParams& S = P.shade;
+	const uint32_t pixel_seed = x + y * (uint32_t)P.width;
+	uint32_t k = 0;            // sample in this launch
+	uint32_t seed = 0;
+	int bounce = 0;
+	bool shadow_phase = false; // current ray is a sun shadow ray
+	V3 light = mk3(0.f, 0.f, 0.f), throughput = mk3(1.f, 1.f, 1.f);
+	V3 fn = mk3(0.f, 0.f, 0.f);
+	RayOD ray;
+	ray.o = mk3(0.f, 0.f, 0.f); ray.d = mk3(0.f, 0.f, 1.f);
+	V3 next_o = ray.o;
+	if (P.n_samples == 0) return acc;
+	seed = pixel_seed * P.frame_first;
+	ray = camera_get_ray<STRICT>(P.cam, x, y, (uint32_t)P.width, (uint32_t)P.height, seed, rtl);
+
+	while (k < P.n_samples) {
+		Hit hit;
+		const bool found = trace_ray_mode<STRICT, 2, STATS>(sc, ray.o, ray.d, FLT_MAX, hit, st, shadow_phase);
+		bool path_done = false;
+		if (shadow_phase) {
+			pc.shadow++;
+			if (!found) light = m::add3(light, m::mul3(S.suncol, throughput));
+			shadow_phase = false;
+		}
+		else {
+			pc.closest++;
+			seed += (uint32_t)bounce;
+			if (!found) {
+				V3 sky = sky_model<STRICT>(ray.d, S.sky_color);
+				light = m::add3(light, m::scale(m::mul3(sky, throughput), S.sky_intensity));
+				path_done = true;
+			}
+			else {
+				const drt_f4 r1 = ld_f4(sc.tris + 3 * (size_t)hit.prim + 1);
+				const uint32_t mat = as_uint(r1.w) & 0x7fffffffu;
+				const drt_f4 mrec = ld_f4(sc.materials + mat);
+				const int tex = (int)as_uint(mrec.w);
+				if (tex < 0) throughput = m::mul3(throughput, mk3(mrec.x, mrec.y, mrec.z));
+				else {
+					V2 tuv = interp_uv<STRICT>(sc, hit.prim, hit.u, hit.v);
+					throughput = m::mul3(throughput, texture_get_pixel<STRICT>(sc, tex, tuv, st));
+				}
+				const drt_f4 s0 = ld_f4(sc.shade + 3 * (size_t)hit.prim);
+				fn = mk3(s0.x, s0.y, s0.z);
+				const V3 pos = m::add3(ray.o, m::scale(ray.d, hit.t));
+				if (m::dot(fn, m::normalize(ray.d)) > 0.f) fn = m::scale(fn, -1.f);
+				next_o = m::add3(pos, m::scale(fn, 0.001f));
+				if (S.enable_sunlight) {
+					ray.o = next_o;
+					ray.d = m::add3(S.sunpos, m::scale(random_unit_vec3<STRICT>(seed, rtl), 1.5f));
+					shadow_phase = true;
+				}
+			}
+		}
+		if (!shadow_phase && !path_done) {
+			// diffuse scatter (RayGen.cuh:133-134), then the loop counter of RayGen.cuh:88
+			ray.o = next_o;
+			ray.d = m::add3(fn, random_unit_sphere_vec3<STRICT>(seed, rtl));
+			bounce++;
+			if (bounce > S.bounce_limit) path_done = true;
+		}
+		if (path_done) {
+			acc = m::add3(acc, post_process<STRICT>(P, light));
+			k++;
+			if (k < P.n_samples) {
+				light = mk3(0.f, 0.f, 0.f); throughput = mk3(1.f, 1.f, 1.f);
+				bounce = 0;
+				seed = pixel_seed * (P.frame_first + k * P.frame_stride);
+				ray = camera_get_ray<STRICT>(P.cam, x, y, (uint32_t)P.width, (uint32_t)P.height, seed, rtl);
+			}
+		}
+	}
+	return acc;
+}
+
 } // namespace drt

@@ -119,10 +119,13 @@ DRT_HD bool alpha_accept(const SceneView& sc, int slot, uint32_t mat, float bu, 
 // Traces one ray. ANYHIT: returns at the first accepted triangle (RayTest semantics: t > 1e-6,
 // unbounded). Otherwise finds the closest accepted triangle with t < tmax.
 // hit.prim is the LEAF-ORDER slot; the canonical id is as_uint(tris[3*slot].w).
-template <bool STRICT, bool ANYHIT, bool STATS>
-DRT_HD bool trace_ray(const SceneView& sc, V3 o, V3 d, float tmax, Hit& hit, TraceStats* st)
+// MODE: 0 = closest hit, 1 = any hit, 2 = decided per ray at run time by `anyhit_rt` (one call site
+// serving both ray kinds keeps a warp converged inside the traversal loop).
+template <bool STRICT, int MODE, bool STATS>
+DRT_HD bool trace_ray_mode(const SceneView& sc, V3 o, V3 d, float tmax, Hit& hit, TraceStats* st, bool anyhit_rt)
 {
 	typedef M<STRICT> m;
+	const bool ANYHIT = MODE == 2 ? anyhit_rt : (MODE == 1);
 	hit.prim = -1;
 	hit.t = tmax;
 	hit.u = 0.f;
@@ -249,6 +252,12 @@ DRT_HD bool trace_ray(const SceneView& sc, V3 o, V3 d, float tmax, Hit& hit, Tra
 		}
 	}
 	return hit.prim >= 0;
+}
+
+template <bool STRICT, bool ANYHIT, bool STATS>
+DRT_HD bool trace_ray(const SceneView& sc, V3 o, V3 d, float tmax, Hit& hit, TraceStats* st)
+{
+	return trace_ray_mode<STRICT, ANYHIT ? 1 : 0, STATS>(sc, o, d, tmax, hit, st, ANYHIT);
 }
 
 } // namespace drt

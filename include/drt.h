@@ -134,6 +134,13 @@ void drt_scene_destroy(drt_scene* scene);
 int drt_renderer_create(int device, drt_renderer** out);
 int drt_renderer_set_stream(drt_renderer* r, void* cuda_stream); /* launch on a caller-owned stream (NULL = own stream) */
 int drt_renderer_set_flags(drt_renderer* r, uint32_t flags);
+/* Kernel selection for measurements: variant 0 = flat state machine (default), 1 = per-sample bounce loop;
+ * block_threads = 0 (default 128) or a multiple of 32 up to 256. Results do not depend on either. */
+int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads);
+void drt_renderer_destroy(drt_renderer* r);
+int drt_renderer_kernel_launches(const drt_renderer* r); /* kernels launched by this renderer so far */
+/* Checkpoint / resume: restore accumulation sums (3 floats / pixel) and the number of samples they hold. */
+int drt_renderer_upload_accum(drt_renderer* r, const float* rgb32f, size_t bytes, uint32_t samples_done);
 /* Sample-range sharding across GPUs: this renderer renders frame indices first, first+stride, ... (default 1, 1). */
 int drt_renderer_set_frame_schedule(drt_renderer* r, uint32_t first_frame, uint32_t stride);
 int drt_renderer_resize(drt_renderer* r, uint32_t width, uint32_t height);

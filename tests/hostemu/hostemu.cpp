@@ -298,6 +298,29 @@ void emu_render(void* h, const drt_camera* cam, const drt_settings* st, int W, i
 	if (counters) memcpy(counters, tot, sizeof(tot));
 }
 
+// Same contract as emu_render, through the flat state machine the production kernel uses.
+void emu_render_flat(void* h, const drt_camera* cam, const drt_settings* st, int W, int H, unsigned first, unsigned stride,
+	unsigned n, int strict, int rtl, float* acc, unsigned long long* counters)
+{
+	EmuScene* s = (EmuScene*)h;
+	RenderParams P = make_params(s, cam, st, W, H);
+	P.frame_first = first; P.frame_stride = stride; P.n_samples = n;
+	unsigned long long c0 = 0, c1 = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : c0, c1)
+	for (int y = 0; y < H; y++) {
+		PathCounters pc;
+		pc.closest = pc.shadow = 0;
+		for (int x = 0; x < W; x++) {
+			float* a = acc + 3 * ((size_t)x + (size_t)y * W);
+			V3 in = mk3(a[0], a[1], a[2]);
+			V3 r = strict ? render_pixel_flat<true, false>(P, x, y, rtl != 0, in, pc, nullptr) : render_pixel_flat<false, false>(P, x, y, rtl != 0, in, pc, nullptr);
+			a[0] = r.x; a[1] = r.y; a[2] = r.z;
+		}
+		c0 += pc.closest; c1 += pc.shadow;
+	}
+	if (counters) { counters[0] = c0; counters[1] = c1; }
+}
+
 void emu_camera_params(const drt_camera* cam, int W, int H, float* out20)
 {
 	CameraParams c = make_camera_params(*cam, W, H);
