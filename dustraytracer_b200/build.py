@@ -67,7 +67,7 @@ def build_libdrt(force=False, verbose=False):
         if verbose and out:
             print(out)
         objs.append(obj)
-    _run([nvcc, "-shared", "-ccbin", _host_cxx(), "-o", LIB] + objs + ["-lz"])
+    _run([nvcc, "-shared", "-ccbin", _host_cxx(), "-Xlinker", "-Bsymbolic", "-o", LIB] + objs + ["-lz"])
     return LIB
 
 
@@ -76,7 +76,7 @@ def build_hostemu(force=False):
     if not force and not _newer(HOSTEMU, _all_csrc() + [src]):
         return HOSTEMU
     os.makedirs(os.path.dirname(HOSTEMU), exist_ok=True)
-    _run([_host_cxx(), "-std=c++17", "-O2", "-fPIC", "-fopenmp", "-ffp-contract=off", "-x", "c++", "-shared", "-o", HOSTEMU,
+    _run([_host_cxx(), "-std=c++17", "-O2", "-fPIC", "-fopenmp", "-ffp-contract=off", "-x", "c++", "-shared", "-Wl,-Bsymbolic", "-o", HOSTEMU,
           src, os.path.join(CSRC, "drt_gltf.cpp"), os.path.join(CSRC, "drt_png.cpp"), "-lz"])
     return HOSTEMU
 

@@ -1,0 +1,220 @@
+"""The C-ABI shared library: loads, exports every symbol include/drt.h declares, struct layouts match the
+reference PODs, host-only entry points work, and device entry points FAIL LOUDLY without a GPU (there is no
+CPU fallback). Also the host-side loader on hand-made glTF/PNG inputs. No compute calls need a GPU here."""
+import ctypes
+import json
+import os
+import re
+import struct
+import zlib
+
+import numpy as np
+import pytest
+
+import oracles as O
+import dustraytracer_b200 as drt
+from dustraytracer_b200 import _lib
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(O.ROOT, "include", "drt.h")).read()
+    declared = set(re.findall(r"\b(drt_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 30
+    handle = ctypes.CDLL(_lib.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(handle, name), "libdrt.so does not export " + name
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+
+
+def test_pod_layouts_match_the_reference():
+    assert ctypes.sizeof(_lib.drt_camera) == 88          # Camera.cuh (measured: SURVEY.md 8a a6)
+    assert ctypes.sizeof(_lib.drt_settings) == 64        # RendererSettings.h
+    assert ctypes.sizeof(_lib.drt_material) == 44        # Material.cuh
+    assert _lib.drt_settings.sunlight_dir.offset == 24 and _lib.drt_settings.sky_intensity.offset == 60
+    assert _lib.drt_camera.position.offset == 32 and _lib.drt_camera.viewheight.offset == 80
+    cam = drt.Camera()
+    assert bytes(cam) == O.default_camera_bytes().tobytes()
+    st = drt.RendererSettings()
+    assert bytes(st) == O.settings_bytes().tobytes()
+
+
+def test_no_cpu_fallback_without_a_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    s = drt.Scene()
+    s.loadGLTFmodel(O.scene_path("cube"))
+    with pytest.raises(drt.DrtError) as e:
+        drt.BVHBuilder().build(s)
+    assert e.value.code == -4
+    with pytest.raises(drt.DrtError):
+        drt.Renderer()
+
+
+def test_error_reporting():
+    s = drt.Scene()
+    with pytest.raises(drt.DrtError) as e:
+        s.loadGLTFmodel("/nonexistent/file.glb")
+    assert e.value.code == -2 and "cannot read" in str(e.value)
+
+
+def _png(px, color_type=None, depth=8, interlace=0, palette=None, trns=None, filters=None):
+    h, w = px.shape[:2]
+    c = 1 if px.ndim == 2 else px.shape[2]
+    if color_type is None:
+        color_type = {1: 0, 2: 4, 3: 2, 4: 6}[c]
+
+    def chunk(tag, data):
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    def rows(img):
+        hh, ww = img.shape[:2]
+        flat = img.reshape(hh, -1)
+        if depth == 16:
+            flat = np.stack([flat >> 8, flat & 255], -1).reshape(hh, -1)
+        elif depth < 8:
+            per = 8 // depth
+            pad = (-flat.shape[1]) % per
+            f2 = np.pad(flat, ((0, 0), (0, pad))).reshape(hh, -1, per)
+            flat = sum(f2[:, :, k].astype(np.uint32) << (8 - depth * (k + 1)) for k in range(per))
+        flat = flat.astype(np.uint8)
+        out = bytearray()
+        bpp = max(1, c * depth // 8)
+        prev = np.zeros(flat.shape[1], np.int32)
+        for y in range(hh):
+            ft = 0 if filters is None else filters[y % len(filters)]
+            cur = flat[y].astype(np.int32)
+            left = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]])
+            ul = np.concatenate([np.zeros(bpp, np.int32), prev[:-bpp]])
+            if ft == 0: enc = cur
+            elif ft == 1: enc = cur - left
+            elif ft == 2: enc = cur - prev
+            elif ft == 3: enc = cur - ((left + prev) >> 1)
+            else:
+                p = left + prev - ul
+                pa, pb, pc = abs(p - left), abs(p - prev), abs(p - ul)
+                pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, ul))
+                enc = cur - pred
+            out += bytes([ft]) + (enc & 255).astype(np.uint8).tobytes()
+            prev = cur
+        return bytes(out)
+
+    if interlace:
+        xs, ys, dx, dy = [0, 4, 0, 2, 0, 1, 0], [0, 0, 4, 0, 2, 0, 1], [8, 8, 4, 4, 2, 2, 1], [8, 8, 8, 4, 4, 2, 2]
+        raw = b"".join(rows(px[ys[p]::dy[p], xs[p]::dx[p]]) for p in range(7) if px[ys[p]::dy[p], xs[p]::dx[p]].size)
+    else:
+        raw = rows(px)
+    out = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, color_type, 0, 0, interlace))
+    if palette is not None:
+        out += chunk(b"PLTE", np.asarray(palette, np.uint8).tobytes())
+    if trns is not None:
+        out += chunk(b"tRNS", bytes(trns))
+    half = len(raw) // 2
+    z = zlib.compress(raw)
+    return out + chunk(b"IDAT", z[:len(z) // 2]) + chunk(b"IDAT", z[len(z) // 2:]) + chunk(b"IEND", b"")
+
+
+def _glb_with_image(png_bytes):
+    pos = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    nrm = np.array([[0, 0, 1]] * 3, np.float32)
+    uv = np.array([[0, 0], [1, 0], [0, 1]], np.float32)
+    idx = np.array([0, 1, 2, 0], np.uint16)  # 4th index = padding of the view to 8 bytes
+    chunks = [pos.tobytes(), nrm.tobytes(), uv.tobytes(), idx.tobytes()[:6] + b"\0\0", png_bytes]
+    views, off = [], 0
+    for i, c in enumerate(chunks):
+        views.append({"buffer": 0, "byteOffset": off, "byteLength": len(c) if i != 3 else 6})
+        off += len(c) + ((4 - len(c) % 4) % 4)
+    binbuf = b"".join(c + b"\0" * ((4 - len(c) % 4) % 4) for c in chunks)
+    j = {"asset": {"version": "2.0"}, "nodes": [{"mesh": 0}],
+         "meshes": [{"primitives": [{"attributes": {"POSITION": 0, "NORMAL": 1, "TEXCOORD_0": 2}, "indices": 3, "material": 0}]}],
+         "materials": [{"pbrMetallicRoughness": {"baseColorFactor": [0.5, 0.25, 1.0, 1.0], "baseColorTexture": {"index": 0}}}],
+         "textures": [{"source": 0}], "images": [{"bufferView": 4, "mimeType": "image/png"}],
+         "accessors": [{"bufferView": 0, "componentType": 5126, "count": 3, "type": "VEC3"},
+                       {"bufferView": 1, "componentType": 5126, "count": 3, "type": "VEC3"},
+                       {"bufferView": 2, "componentType": 5126, "count": 3, "type": "VEC2"},
+                       {"bufferView": 3, "componentType": 5123, "count": 3, "type": "SCALAR"}],
+         "bufferViews": views, "buffers": [{"byteLength": len(binbuf)}]}
+    js = json.dumps(j).encode()
+    js += b" " * ((4 - len(js) % 4) % 4)
+    return struct.pack("<III", 0x46546C67, 2, 28 + len(js) + len(binbuf)) + struct.pack("<II", len(js), 0x4E4F534A) + js + \
+        struct.pack("<II", len(binbuf), 0x004E4942) + binbuf
+
+
+def _load_texture(tmp_path, png_bytes):
+    p = tmp_path / "t.glb"
+    p.write_bytes(_glb_with_image(png_bytes))
+    s = drt.Scene()
+    s.loadGLTFmodel(str(p))
+    return s
+
+
+def test_png_decoder_variants(tmp_path):
+    rng = np.random.RandomState(3)
+    for c in (1, 2, 3, 4):
+        px = rng.randint(0, 256, (13, 17, c)).astype(np.uint8)
+        for interlace in (0, 1):
+            s = _load_texture(tmp_path, _png(px if c > 1 else px[:, :, 0], interlace=interlace, filters=[0, 1, 2, 3, 4]))
+            got = s.texture(0)
+            assert got.shape == (13, 17, c) and np.array_equal(got, px)
+    # 16-bit keeps the high byte (stb convention)
+    px16 = rng.randint(0, 65536, (5, 7, 3)).astype(np.uint32)
+    s = _load_texture(tmp_path, _png(px16, color_type=2, depth=16))
+    assert np.array_equal(s.texture(0), (px16 >> 8).astype(np.uint8))
+    # palette (+tRNS -> 4 channels), low bit depth gray scaled to 0..255
+    pal = rng.randint(0, 256, (4, 3)).astype(np.uint8)
+    idx = rng.randint(0, 4, (6, 9)).astype(np.uint8)
+    s = _load_texture(tmp_path, _png(idx, color_type=3, depth=2, palette=pal))
+    assert np.array_equal(s.texture(0), pal[idx])
+    s = _load_texture(tmp_path, _png(idx, color_type=3, depth=2, palette=pal, trns=[0, 128]))
+    got = s.texture(0)
+    assert got.shape[2] == 4 and np.array_equal(got[:, :, :3], pal[idx]) and np.array_equal(got[:, :, 3], np.array([0, 128, 255, 255], np.uint8)[idx])
+    g2 = rng.randint(0, 4, (4, 10)).astype(np.uint8)
+    s = _load_texture(tmp_path, _png(g2, color_type=0, depth=2))
+    assert np.array_equal(s.texture(0)[:, :, 0], g2 * 0x55)
+
+
+def test_loader_reference_quirks(tmp_path):
+    s = _load_texture(tmp_path, _png(np.full((2, 2, 3), 200, np.uint8)))
+    t = s.triangles()
+    assert t.shape == (1, 32)
+    assert np.allclose(t[0, 28:31], (0, 0, 1))                       # face normal oriented to the vertex normals
+    assert np.allclose(t[0, 0:3], (1 / 3, 1 / 3, 0))                  # centroid
+    m = s.materials()[0]
+    assert tuple(m.albedo) == (0.5, 0.25, 1.0) and m.albedo_texture_index == 0 and m.metallic == 1
+    # external .gltf + .bin + data: URI image
+    import base64
+    glb = _glb_with_image(_png(np.full((2, 2, 4), 9, np.uint8)))
+    jlen = struct.unpack("<I", glb[12:16])[0]
+    j = json.loads(glb[20:20 + jlen])
+    binbuf = glb[28 + jlen:]
+    png_view = j["bufferViews"][4]
+    png = binbuf[png_view["byteOffset"]:png_view["byteOffset"] + png_view["byteLength"]]
+    j["buffers"][0]["uri"] = "geo%20metry.bin"
+    j["images"][0] = {"uri": "data:image/png;base64," + base64.b64encode(png).decode()}
+    (tmp_path / "geo metry.bin").write_bytes(binbuf)
+    (tmp_path / "scene.gltf").write_text(json.dumps(j))
+    s2 = drt.Scene()
+    s2.loadGLTFmodel(str(tmp_path / "scene.gltf"))
+    assert np.array_equal(s2.triangles(), t) and s2.texture(0).shape == (2, 2, 4)
+    # u32 indices are rejected with the reference's limitation named (Scene.cu:161)
+    j["accessors"][3]["componentType"] = 5125
+    (tmp_path / "bad.gltf").write_text(json.dumps(j))
+    with pytest.raises(drt.DrtError) as e:
+        drt.Scene().loadGLTFmodel(str(tmp_path / "bad.gltf"))
+    assert e.value.code == -3
+    # a missing TEXCOORD_0 silently reads accessor 0 like the reference (Scene.cu:129-131)
+    j["accessors"][3]["componentType"] = 5123
+    del j["meshes"][0]["primitives"][0]["attributes"]["TEXCOORD_0"]
+    (tmp_path / "nouv.gltf").write_text(json.dumps(j))
+    s3 = drt.Scene()
+    s3.loadGLTFmodel(str(tmp_path / "nouv.gltf"))
+    t3 = s3.triangles()
+    assert np.array_equal(t3[0, [10, 11]], t[0, [4, 5]])  # uv0 = first 8 bytes of the POSITION view
+
+
+def test_from_triangles_host_side():
+    pos = np.array([[[0, 0, 0], [1, 0, 0], [0, 1, 0]], [[0, 0, 1], [0, 1, 1], [1, 0, 1]]], np.float32)
+    s = drt.Scene.from_triangles(pos)
+    t = s.triangles()
+    assert t.shape == (2, 32) and s.stats()["materials"] == 1
+    assert np.allclose(t[0, 28:31], (0, 0, 1)) and np.allclose(t[1, 28:31], (0, 0, -1))

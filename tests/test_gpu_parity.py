@@ -1,0 +1,272 @@
+"""Parity of the CUDA path (through the C ABI, libdrt.so) against the oracle. Needs a B200: run with -m gpu.
+
+Bars (BASELINE.json north_star):
+  * primary-ray hit triangle ids: bit-exact against the reference (strict mode also reproduces t, u, v and
+    whole accumulated images bit for bit; exact-t ties are counted and logged);
+  * production (fused-multiply-add, hardware rsqrt) mode: ids equal except logged near-tie pixels
+    (|dt| <= 1e-4 * t), converged radiance within RMSE_TOL per pixel of the oracle at equal sample count.
+"""
+import os
+import zlib
+
+import numpy as np
+import pytest
+
+import oracles as O
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(O.ROOT, "tests", "golden")
+SCENES = ["cornell_box", "room", "dense_monkey", "valorant_ghost", "animemaid", "mc_transparency_test", "bvhsplit_test", "cube"]
+RMSE_TOL = 0.05      # LDR units (display values in [0,1]) at 64 spp; two independent 64-spp estimates differ by ~0.03
+MEAN_TOL = 0.004     # bias check: mean over the image of the signed difference
+STRICT = 1 | 2       # DRT_FLAG_STRICT | DRT_FLAG_HOST_ARG_ORDER (the oracle is g++-compiled)
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def crc(a):
+    return zlib.crc32(np.ascontiguousarray(a).tobytes()) & 0xFFFFFFFF
+
+
+@pytest.fixture(scope="module")
+def drt():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import dustraytracer_b200 as d
+    return d
+
+
+_scene_cache = {}
+
+
+def gpu_scene(drt, name):
+    if name not in _scene_cache:
+        s = drt.Scene()
+        s.loadGLTFmodel(O.scene_path(name))
+        drt.BVHBuilder().buildIterative(s)
+        _scene_cache[name] = s
+    return _scene_cache[name]
+
+
+def camera_from(drt, cam_f32):
+    import ctypes
+    cam = drt.Camera()
+    ctypes.memmove(ctypes.addressof(cam), cam_f32.tobytes(), 88)
+    return cam
+
+
+def settings_from(drt, st_bytes):
+    import ctypes
+    st = drt.RendererSettings()
+    ctypes.memmove(ctypes.addressof(st), st_bytes.tobytes(), 64)
+    return st
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_primary_hits_bit_exact(drt, name):
+    g = np.load(os.path.join(GOLDEN, "scene_%s.npz" % name))
+    scene = gpu_scene(drt, name)
+    st = scene.stats()
+    assert st["wide_nodes"] >= 1 and st["build_ms"] > 0
+    pw, ph = [int(x) for x in g["primary_size"]]
+    r = drt.Renderer(flags=STRICT)
+    r.ResizeBuffer(pw, ph)
+    hits = r.trace_primary(camera_from(drt, g["camera"]), scene, 1)
+    assert np.array_equal(hits["prim_id"], g["prim_id"]), "%d id mismatches" % (hits["prim_id"] != g["prim_id"]).sum()
+    assert crc(hits["t"]) == int(g["crc_t"]) and crc(hits["u"]) == int(g["crc_u"]) and crc(hits["v"]) == int(g["crc_v"])
+    c = r.counters()
+    print("%s: %d exact-t tie events over %d rays, max stack %d" % (name, c["tie_events"], pw * ph, c["max_stack"]))
+    # production arithmetic: same ids except logged near-ties
+    r.set_flags(2)
+    fast = r.trace_primary(camera_from(drt, g["camera"]), scene, 1)
+    diff = np.flatnonzero(fast["prim_id"] != g["prim_id"])
+    tg = np.full(pw * ph, -1, np.float32)
+    tg.reshape(ph, pw)[::4, ::4] = g["tuv_stride4"][0]
+    print("%s: production-mode id differences: %d of %d pixels" % (name, diff.size, pw * ph))
+    assert diff.size <= max(2, int(2e-5 * pw * ph))
+    sub = fast["t"].reshape(ph, pw)[::4, ::4]
+    same = (fast["prim_id"].reshape(ph, pw)[::4, ::4] == g["prim_id"].reshape(ph, pw)[::4, ::4]) & (g["tuv_stride4"][0] > 0)
+    assert np.all(np.abs(sub[same] - g["tuv_stride4"][0][same]) <= 1e-4 * g["tuv_stride4"][0][same])
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("name", SCENES)
+def test_accumulated_image_bit_exact(drt, name, variant):
+    g = np.load(os.path.join(GOLDEN, "scene_%s.npz" % name))
+    scene = gpu_scene(drt, name)
+    rw, rh, frames, sun, bounces = [int(x) for x in g["render_size"]]
+    r = drt.Renderer(flags=STRICT)
+    r.set_tuning(variant, 0)
+    r.m_RendererSettings = settings_from(drt, g["settings"])
+    r.ResizeBuffer(rw, rh)
+    cam = camera_from(drt, g["camera"])
+    r.Render(cam, scene, frames)           # one batched launch
+    acc = r.readback(drt.DRT_ACCUM_RGB32F).reshape(-1)
+    assert np.array_equal(bits(acc), bits(g["acc"])), "max abs diff %g" % np.abs(acc - g["acc"]).max()
+    c = r.counters()
+    assert c["closest_rays"] == int(g["rays"][0]) and c["shadow_rays"] == int(g["rays"][1])
+    assert r.getSampleCount() == frames + 1
+    disp = r.readback(drt.DRT_RGBA32F)
+    assert np.array_equal(bits(disp[:, :, :3].reshape(-1)), bits(g["acc"] / np.float32(frames))) and np.all(disp[:, :, 3] == 1)
+    # frame by frame, like the reference's one launch per frame
+    r.resetAccumulationBuffer()
+    assert r.getSampleCount() == 1
+    for _ in range(frames):
+        r.Render(cam, scene)
+    assert np.array_equal(bits(r.readback(drt.DRT_ACCUM_RGB32F).reshape(-1)), bits(g["acc"]))
+
+
+@pytest.mark.parametrize("name,sun,bounces", [("room", True, 8), ("animemaid", True, 2), ("dense_monkey", False, 4)])
+def test_production_mode_converged_radiance(drt, name, sun, bounces):
+    """Production arithmetic + nvcc argument order against the oracle at equal sample count."""
+    W, H, spp = 128, 72, 64
+    orc = O.best_oracle()
+    cam_f = O.default_camera_bytes()
+    st_b = O.settings_bytes(sun=sun, bounces=bounces)
+    if orc.kind == "reference":
+        oh = orc.load(O.scene_path(name))
+    else:
+        import dustraytracer_b200 as d
+        s = d.Scene()
+        s.loadGLTFmodel(O.scene_path(name))
+        mats = np.frombuffer(b"".join(bytes(m) for m in s.materials()), np.uint32).reshape(-1, 11).copy()
+        oh = orc.create(s.triangles(), mats, [s.texture(i) for i in range(s.stats()["textures"])])
+    ref, _, _ = orc.render(oh, cam_f, st_b, W, H, 1, spp)
+    ref = ref.reshape(H, W, 3) / spp
+    scene = gpu_scene(drt, name)
+    r = drt.Renderer()
+    r.m_RendererSettings = settings_from(drt, st_b)
+    r.ResizeBuffer(W, H)
+    r.Render(camera_from(drt, cam_f), scene, spp)
+    img = r.readback(drt.DRT_RGBA32F)[:, :, :3]
+    rmse = float(np.sqrt(np.mean((img - ref) ** 2)))
+    bias = float(np.mean(img - ref))
+    print("%s: production vs %s oracle at %d spp: RMSE %.4f, mean diff %+.5f" % (name, orc.kind, spp, rmse, bias))
+    assert rmse <= RMSE_TOL and abs(bias) <= MEAN_TOL
+    orc.free(oh)
+
+
+def test_full_size_properties(drt):
+    """BASELINE config-3 size (room, 1920x1080, sun, 8 bounces): determinism, batching invariance, sample-range
+    sharding = partition of the frames, ray accounting."""
+    scene = gpu_scene(drt, "room")
+    W, H = 1920, 1080
+    cam = drt.Camera()
+    st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=8, max_samples=100000)
+
+    def run(first, stride, n, batch, flags=0, variant=0):
+        r = drt.Renderer(flags=flags)
+        r.set_tuning(variant, 0)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(W, H)
+        r.set_frame_schedule(first, stride)
+        done = 0
+        while done < n:
+            r.Render(cam, scene, min(batch, n - done))
+            done += min(batch, n - done)
+        return r.readback(drt.DRT_ACCUM_RGB32F), r.counters()
+
+    a, ca = run(1, 1, 4, 4)
+    b, cb = run(1, 1, 4, 1)
+    assert np.array_equal(bits(a), bits(b)) and ca == cb, "batched launch == one launch per frame"
+    a2, _ = run(1, 1, 4, 4)
+    assert np.array_equal(bits(a), bits(a2)), "deterministic"
+    assert 4 * W * H <= ca["closest_rays"] <= 9 * 4 * W * H and ca["shadow_rays"] <= ca["closest_rays"]
+    s0, c0 = run(1, 2, 2, 2)
+    s1, c1 = run(2, 2, 2, 2)
+    assert c0["closest_rays"] + c1["closest_rays"] == ca["closest_rays"]
+    assert np.abs((s0 + s1) - a).max() <= 4 * np.finfo(np.float32).eps * np.abs(a).max()
+    # strict arithmetic: both kernel variants agree bit for bit at full size
+    v0, _ = run(1, 1, 2, 2, flags=STRICT, variant=0)
+    v1, _ = run(1, 1, 2, 2, flags=STRICT, variant=1)
+    assert np.array_equal(bits(v0), bits(v1))
+    assert np.isfinite(a).all() and a.min() >= 0
+
+
+def test_renderer_semantics(drt):
+    scene = gpu_scene(drt, "cornell_box")
+    r = drt.Renderer()
+    r.ResizeBuffer(64, 48)
+    cam = drt.Camera()
+    r.m_RendererSettings.max_samples = 4          # Renderer.cu:82: stops when the frame index reaches max_samples
+    for _ in range(10):
+        r.Render(cam, scene)
+    assert r.getSampleCount() == 4
+    r.Render(cam, scene, 100)
+    assert r.getSampleCount() == 4
+    img3 = r.readback(drt.DRT_RGBA32F)
+    r.ResizeBuffer(64, 48)                        # unchanged size: no reset (Renderer.cu:30)
+    assert r.getSampleCount() == 4
+    r.ResizeBuffer(32, 24)
+    assert r.getSampleCount() == 1 and r.getBufferWidth() == 32
+    r.ResizeBuffer(64, 48)
+    r.m_RendererSettings.max_samples = 500
+    r.Render(cam, scene, 3)
+    assert np.array_equal(bits(r.readback(drt.DRT_RGBA32F)), bits(img3))
+    rgba8 = r.readback(drt.DRT_RGBA8)
+    assert rgba8.dtype == np.uint8 and np.all(rgba8[:, :, 3] == 255)
+    assert np.abs(rgba8[:, :, :3].astype(np.float32) - np.clip(img3[:, :, :3], 0, 1) * 255).max() <= 0.5001
+    # checkpoint / resume
+    acc = r.readback(drt.DRT_ACCUM_RGB32F)
+    r2 = drt.Renderer()
+    r2.ResizeBuffer(64, 48)
+    r2.upload_accum(acc, 3)
+    r.Render(cam, scene, 2)
+    r2.Render(cam, scene, 2)
+    assert np.array_equal(bits(r.readback(drt.DRT_ACCUM_RGB32F)), bits(r2.readback(drt.DRT_ACCUM_RGB32F)))
+    # debug views run through the per-sample loop
+    r.m_RendererSettings.render_mode = 1
+    r.m_RendererSettings.debug_mode = 1
+    r.resetAccumulationBuffer()
+    r.Render(cam, scene)
+    n = r.readback(drt.DRT_RGBA32F)[:, :, :3]
+    lens = np.linalg.norm(n, axis=2)
+    assert np.all((np.abs(lens - 1) < 1e-3) | (lens > 1.0))   # unit normals on hits, sky elsewhere
+    with pytest.raises(drt.DrtError):
+        drt.Renderer().Render(cam, scene)     # no buffer yet
+
+
+def test_gpu_builder_on_synthetic_soups(drt):
+    emu = O.HostEmu()
+    mat = np.zeros((1, 11), np.uint32)
+    mat.view(np.float32)[0, 0:3] = 0.8
+    mat.view(np.int32)[0, 6] = -1
+    for n in (0, 1, 3, 4, 33, 1000, 200000):
+        rng = np.random.RandomState(n + 1)
+        c = rng.uniform(-10, 10, (n, 1, 3))
+        pos = (c + rng.uniform(-0.4, 0.4, (n, 3, 3))).astype(np.float32)
+        s = drt.Scene.from_triangles(pos)
+        s.build_bvh()
+        if n:
+            ids = s.leaf_triangles().view(np.uint32)[:, 3]
+            assert np.array_equal(np.sort(ids), np.arange(n, dtype=np.uint32)), "every triangle exactly once"
+        cam = drt.Camera(pos=(0, 0, 30))
+        r = drt.Renderer(flags=STRICT)
+        r.ResizeBuffer(160, 90)
+        hits = r.trace_primary(cam, s, 1)
+        eh = emu.from_triangles(pos, mat)
+        pid, t, u, v, _ = emu.trace_primary(eh, np.frombuffer(bytes(cam), np.float32).copy(), 160, 90, 1, strict=True, rtl=True)
+        emu.free(eh)
+        # different tree instances (atomics order), same winner: ties go to the lowest canonical id
+        assert np.array_equal(hits["prim_id"], pid) and np.array_equal(bits(hits["t"]), bits(t)), n
+        print("soup %d: build %.3f ms, %d wide nodes, hit fraction %.3f" % (n, s.stats()["build_ms"], s.stats()["wide_nodes"], (pid >= 0).mean()))
+    # degenerate: identical centroids -> median splits, still a valid tree
+    tri = np.array([[[0, 0, 0], [1, 0, 0], [0, 1, 0]]], np.float32)
+    s = drt.Scene.from_triangles(np.repeat(tri, 1000, 0))
+    s.build_bvh()
+    assert np.array_equal(np.sort(s.leaf_triangles().view(np.uint32)[:, 3]), np.arange(1000, dtype=np.uint32))
+
+
+def test_stats_counters(drt):
+    scene = gpu_scene(drt, "room")
+    r = drt.Renderer(flags=4)
+    r.m_RendererSettings = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=8)
+    r.ResizeBuffer(240, 135)
+    r.Render(drt.Camera(), scene, 2)
+    c = r.counters()
+    rays = c["closest_rays"] + c["shadow_rays"]
+    assert rays > 0 and c["node_visits"] >= rays and c["tri_tests"] > 0 and c["max_stack"] <= 48
+    print("room: %.2f wide-node visits/ray, %.2f triangle tests/ray" % (c["node_visits"] / rays, c["tri_tests"] / rays))
