@@ -35,6 +35,10 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 WORKLOAD = {
     "scene": "room.glb", "width": 1920, "height": 1080, "spp": 256, "bounces": 8, "sun": True,
 }
+if os.environ.get("DRT_BENCH_SPP"):  # profiling runs under ncu only: a shorter launch of the same kernel
+    WORKLOAD["spp"] = int(os.environ["DRT_BENCH_SPP"])
+CPU_SAMPLE_FRAMES = 128   # cpu_baseline leg: ~10-20 s on the GPU box's host cores
+REF_STEP_FRAMES = 32      # --impl reference: samples per pixel rendered per step (bounded sample of the 256)
 SCENE_PATH = os.path.join(ROOT, "tests", "golden", "scenes", WORKLOAD["scene"])
 
 
@@ -123,23 +127,23 @@ def run_reference(args, rank):
     orc, oh = oracle_scene()
     cores = orc.max_threads()
     for w in range(args.warmup):
-        cpu_reference_step(orc, oh, 1 + w)
+        cpu_reference_step(orc, oh, 1 + w * REF_STEP_FRAMES, frames=REF_STEP_FRAMES)
     rays_total, sec_total = 0, 0.0
     t0 = time.perf_counter()
     for k in range(args.steps):
-        rays, sec = cpu_reference_step(orc, oh, 1 + args.warmup + k)
+        rays, sec = cpu_reference_step(orc, oh, 1 + (args.warmup + k) * REF_STEP_FRAMES, frames=REF_STEP_FRAMES)
         rays_total += rays
         sec_total += sec
     wall = time.perf_counter() - t0
     mrays = rays_total / sec_total / 1e6
-    samples = WORKLOAD["width"] * WORKLOAD["height"] * args.steps / sec_total
-    sample_desc = "1 of the 256 samples per pixel of the 1920x1080 frame per step (frame index = step), OpenMP over rows"
+    samples = WORKLOAD["width"] * WORKLOAD["height"] * args.steps * REF_STEP_FRAMES / sec_total
+    sample_desc = "%d of the 256 samples per pixel of the 1920x1080 frame per step, OpenMP over rows" % REF_STEP_FRAMES
     line = {
         "impl": "reference", "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * sec_total / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic camera path over the bundled room scene (fixture re-muxed from the reference model)",
         "samples_per_s": samples,
-        "config": {"workload": "room.glb 1920x1080, 8 bounces, sun shadow rays; CPU arm: 1 spp per step", **WORKLOAD},
+        "config": {"workload": "room.glb 1920x1080, 8 bounces, sun shadow rays; CPU arm: %d spp per step" % REF_STEP_FRAMES, **WORKLOAD},
         "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": cores, "kind": orc.kind, "sample": sample_desc},
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": wall,
@@ -270,9 +274,10 @@ def run_ours(args, rank, world, local_rank):
                     "note": "scene is cache resident (42 KB): the binding roofline is SM issue rate, see profiles/ and DESIGN.md"}
         # ---- CPU baseline: bounded sample on the host cores ----
         orc, oh = oracle_scene()
-        crays, csec = cpu_reference_step(orc, oh, 1, frames=1)
+        crays, csec = cpu_reference_step(orc, oh, 1, frames=CPU_SAMPLE_FRAMES)
         cpu = {"value": crays / csec / 1e6, "unit": "Mrays/s", "cores": orc.max_threads(), "kind": orc.kind,
-               "sample": "1 of the 256 samples per pixel (frame index 1) of the same 1920x1080 frame, %.1f s" % csec}
+               "sample": "%d of the 256 samples per pixel (frame indices 1..%d) of the same 1920x1080 frame, %.1f s"
+                         % (CPU_SAMPLE_FRAMES, CPU_SAMPLE_FRAMES, csec)}
         value = total_rays / (max_ms * 1e-3) / 1e6
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
