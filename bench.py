@@ -180,7 +180,7 @@ def run_ours(args, rank, world, local_rank):
     cam = drt.Camera()
     r = drt.Renderer(device=local_rank)
     r.m_RendererSettings = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=WORKLOAD["bounces"], max_samples=1 << 30)
-    r.set_tuning(int(os.environ.get("DRT_VARIANT", "0")), int(os.environ.get("DRT_BLOCK", "0")))
+    r.set_tuning(int(os.environ.get("DRT_VARIANT", "2")), int(os.environ.get("DRT_BLOCK", "0")))
     r.ResizeBuffer(W, H)
     stream = torch.cuda.current_stream(dev)
     r.set_stream(stream.cuda_stream)

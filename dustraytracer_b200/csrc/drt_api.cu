@@ -8,6 +8,8 @@
 #include <cuda_runtime.h>
 
 #include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -15,6 +17,9 @@
 #include "drt_host.h"
 #include "drt_kernels.h"
 #include "drt_params.h"
+#include "drt_phased.cuh"
+
+#define DRT_F32_NODE_LIMIT 65536 // expanded nodes are kept for scenes up to this many wide nodes (16 MB)
 
 namespace drt {
 
@@ -89,6 +94,7 @@ struct drt_scene {
 	int device = -1;
 	bool built = false;
 	DevBuf<WideNode> nodes;
+	DevBuf<drt_f4> nodes_f32;
 	DevBuf<drt_f4> tris, shade, materials;
 	DevBuf<TexDesc> texdesc;
 	DevBuf<uint32_t> texels;
@@ -111,7 +117,8 @@ struct drt_renderer {
 	uint32_t samples_done = 0;  // samples accumulated by THIS renderer
 	uint32_t first_frame = 1, stride = 1;
 	uint32_t flags = 0;
-	int variant = 0, block_threads = 0;
+	int variant = 2, block_threads = 0;
+	int sched_bias[3] = { 0, 0, 0 };
 	int kernel_launches = 0;
 };
 
@@ -361,10 +368,16 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* /*par
 		// keep only the wide nodes that exist
 		DRT_CUDA(scene->nodes.alloc((size_t)res.wide_nodes));
 		DRT_CUDA(cudaMemcpyAsync(scene->nodes.p, wide_tmp.p, (size_t)res.wide_nodes * sizeof(WideNode), cudaMemcpyDeviceToDevice, stream));
+		// cache-resident scenes also get the de-quantised 256-byte nodes (issue-bound regime, drt_phased.cuh)
+		scene->nodes_f32.release();
+		if (res.wide_nodes <= DRT_F32_NODE_LIMIT) {
+			DRT_CUDA(scene->nodes_f32.alloc((size_t)res.wide_nodes * DRT_F32NODE_F4));
+			DRT_CUDA(launch_expand_nodes(scene->nodes.p, scene->nodes_f32.p, res.wide_nodes, stream));
+		}
 		DRT_CUDA(cudaStreamSynchronize(stream));
 	}
 	else {
-		scene->nodes.release(); scene->tris.release(); scene->shade.release();
+		scene->nodes.release(); scene->nodes_f32.release(); scene->tris.release(); scene->shade.release();
 		DRT_CUDA(cudaStreamSynchronize(stream));
 	}
 
@@ -372,12 +385,13 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* /*par
 	v.nodes = (const drt_u4*)scene->nodes.p;
 	v.tris = scene->tris.p; v.shade = scene->shade.p; v.materials = scene->materials.p;
 	v.textures = scene->texdesc.p; v.texels = scene->texels.p;
+	v.nodes_f32 = scene->nodes_f32.p;
 	v.num_tris = (int32_t)n; v.num_nodes = res.wide_nodes; v.num_materials = (int32_t)mats.size(); v.num_textures = (int32_t)texdesc.size();
 	scene->stats.wide_nodes = (uint64_t)res.wide_nodes;
 	scene->stats.bvh2_nodes = (uint64_t)res.bvh2_nodes;
 	scene->stats.bvh_levels = (uint64_t)res.levels;
 	scene->stats.build_ms = build_ms;
-	scene->stats.device_bytes = scene->nodes.bytes() + scene->tris.bytes() + scene->shade.bytes() + scene->materials.bytes()
+	scene->stats.device_bytes = scene->nodes.bytes() + scene->nodes_f32.bytes() + scene->tris.bytes() + scene->shade.bytes() + scene->materials.bytes()
 		+ scene->texdesc.bytes() + scene->texels.bytes();
 	scene->built = true;
 	return DRT_OK;
@@ -427,6 +441,7 @@ extern "C" int drt_renderer_create(int device, drt_renderer** out)
 	if (e == cudaSuccess) e = cudaMemset(r->counters.p, 0, sizeof(Counters));
 	if (e != cudaSuccess) { delete r; return fail(DRT_ERR_CUDA, std::string("drt_renderer_create: ") + cudaGetErrorString(e)); }
 	r->stream = r->own_stream;
+	if (const char* b = getenv("DRT_SCHED_BIAS")) sscanf(b, "%d,%d,%d", &r->sched_bias[0], &r->sched_bias[1], &r->sched_bias[2]); // measurement knob
 	*out = r;
 	return DRT_OK;
 }
@@ -461,7 +476,7 @@ extern "C" int drt_renderer_set_flags(drt_renderer* r, uint32_t flags)
 extern "C" int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads)
 {
 	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: null renderer");
-	if (variant < 0 || variant > 1 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
+	if (variant < 0 || variant > 3 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
 	r->variant = variant; r->block_threads = block_threads;
 	return DRT_OK;
 }
@@ -530,6 +545,7 @@ static LaunchConfig launch_config(const drt_renderer* r)
 	cfg.rtl = (r->flags & DRT_FLAG_HOST_ARG_ORDER) != 0;
 	cfg.stats = (r->flags & DRT_FLAG_STATS) != 0;
 	cfg.variant = r->variant; cfg.block_threads = r->block_threads;
+	for (int i = 0; i < 3; i++) cfg.sched_bias[i] = r->sched_bias[i];
 	return cfg;
 }
 

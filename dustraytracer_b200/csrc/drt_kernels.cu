@@ -8,9 +8,13 @@
 //                              16-byte display write per pixel per LAUNCH instead of 40 B per sample.
 //   variant 1  k_render_loop   one thread per pixel, sample loop around the reference-shaped bounce loop
 //                              (path_radiance); also serves the debug views.
+//   variant 2  phased          per-warp phase voting over NODE / TRI / SHADE steps (drt_phased.cuh), expanded
+//                              fp32 nodes when the scene has them, else compressed nodes  [default]
+//   variant 3  phased, Q8      the same on the compressed nodes regardless of scene size
 // Warps cover 8x4 pixel tiles (coherent primary rays); blocks are rows of such tiles.
 #include "drt_kernels.h"
 #include "drt_shade.cuh"
+#include "drt_phased.cuh"
 
 namespace drt {
 
@@ -52,7 +56,8 @@ __device__ __forceinline__ void flush_counters(Counters* c, const PathCounters& 
 }
 
 template <bool STRICT, bool STATS, int VARIANT>
-__global__ void __launch_bounds__(256) k_render(const __grid_constant__ RenderParams P, const bool rtl, const int warps_per_block)
+__global__ void __launch_bounds__(256) k_render(const __grid_constant__ RenderParams P, const bool rtl, const int warps_per_block,
+	const PhasedTuning tune)
 {
 	int x, y;
 	bool valid;
@@ -62,7 +67,18 @@ __global__ void __launch_bounds__(256) k_render(const __grid_constant__ RenderPa
 	TraceStats ts;
 	ts.nodes = ts.tris = ts.ties = ts.alpha = ts.max_stack = ts.clamps = 0;
 	TraceStats* st = STATS ? &ts : nullptr;
-	if (valid) {
+	if (VARIANT >= 2) {
+		// every lane of the warp takes part in the vote, valid pixel or not
+		const size_t p = (size_t)x + (size_t)y * (size_t)P.width;
+		V3 acc = mk3(0.f, 0.f, 0.f);
+		if (valid) { const float4 a4 = P.accum[p]; acc = mk3(a4.x, a4.y, a4.z); }
+		acc = render_warp_phased<STRICT, STATS, VARIANT == 2 ? NODE_FMT_F32 : NODE_FMT_Q8>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st);
+		if (valid) {
+			P.accum[p] = make_float4(acc.x, acc.y, acc.z, 0.f);
+			P.display[p] = make_float4(acc.x / P.total_samples, acc.y / P.total_samples, acc.z / P.total_samples, 1.f);
+		}
+	}
+	else if (valid) {
 		const size_t p = (size_t)x + (size_t)y * (size_t)P.width;
 		const float4 a4 = P.accum[p];
 		V3 acc = mk3(a4.x, a4.y, a4.z);
@@ -137,6 +153,13 @@ __global__ void k_pack_rgb32f(float* out, const float4* accum, int n)
 	out[3 * (size_t)i] = a.x; out[3 * (size_t)i + 1] = a.y; out[3 * (size_t)i + 2] = a.z;
 }
 
+__global__ void k_expand_nodes(const WideNode* wide, drt_f4* out, int n)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	expand_wide_node(wide[i], out + (size_t)DRT_F32NODE_F4 * i);
+}
+
 // ---- builder passes: one thread per element, bodies in drt_build.cuh ----
 template <int PASS>
 __global__ void __launch_bounds__(256) k_build(const BuildArrays A, const int* idx_final, int a, int b, int n)
@@ -158,8 +181,16 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	const int wpb = threads / 32;
 	const long long tiles = (long long)((P.width + 7) / 8) * ((P.height + 3) / 4);
 	const unsigned blocks = (unsigned)((tiles + wpb - 1) / wpb);
-	if (cfg.variant == 1) k_render<STRICT, STATS, 1><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb);
-	else k_render<STRICT, STATS, 0><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb);
+	PhasedTuning tune;
+	tune.bias_node = cfg.sched_bias[0]; tune.bias_tri = cfg.sched_bias[1]; tune.bias_shade = cfg.sched_bias[2];
+	// the phased kernels implement NORMALMODE; the debug views go through the reference-shaped loop
+	int variant = cfg.variant;
+	if (variant >= 2 && P.shade.render_mode != DRT_RENDER_NORMAL) variant = 1;
+	if (variant == 2 && P.scene.nodes_f32 == nullptr) variant = 3;
+	if (variant == 3) k_render<STRICT, STATS, 3><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+	else if (variant == 2) k_render<STRICT, STATS, 2><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+	else if (variant == 1) k_render<STRICT, STATS, 1><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+	else k_render<STRICT, STATS, 0><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	return cudaGetLastError();
 }
 
@@ -201,6 +232,13 @@ cudaError_t launch_pack_rgb32f(float* out, const drt_f4* accum, int n, cudaStrea
 {
 	if (n <= 0) return cudaSuccess;
 	k_pack_rgb32f<<<(n + 255) / 256, 256, 0, s>>>(out, accum, n);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_expand_nodes(const WideNode* wide, drt_f4* out, int n, cudaStream_t s)
+{
+	if (n <= 0) return cudaSuccess;
+	k_expand_nodes<<<(n + 127) / 128, 128, 0, s>>>(wide, out, n);
 	return cudaGetLastError();
 }
 

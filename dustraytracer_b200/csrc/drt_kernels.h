@@ -10,11 +10,13 @@ struct LaunchConfig {
 	bool strict = false;  // DRT_FLAG_STRICT
 	bool rtl = false;     // DRT_FLAG_HOST_ARG_ORDER
 	bool stats = false;   // DRT_FLAG_STATS
-	int variant = 0;      // render kernel variant (see drt_kernels.cu); 0 = default
+	int variant = 2;      // render kernel variant (see drt_kernels.cu); 2 = default
+	int sched_bias[3] = { 0, 0, 0 }; // phased kernels: vote bias of NODE / TRI / SHADE
 	int block_threads = 0; // 0 = variant default
 };
 
 cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s);
+cudaError_t launch_expand_nodes(const WideNode* wide, drt_f4* out_f32, int n, cudaStream_t s);
 cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches);
 cudaError_t launch_trace_primary(const RenderParams& P, uint32_t frame_index, Hit* out_dev, const LaunchConfig& cfg, cudaStream_t s);
 cudaError_t launch_resolve(drt_f4* display, const drt_f4* accum, int n_pixels, float total_samples, cudaStream_t s);

@@ -1,0 +1,499 @@
+// drt_phased.cuh -- the path loop as per-lane PHASE STEPS, scheduled per warp by vote.
+//
+// Same per-lane arithmetic as drt_trace.cuh / drt_shade.cuh (and therefore the same results as the
+// reference's RayGen -> TraceRay/RayTest -> traverseBVH* -> Intersection chain, RayGen.cuh:63-172,
+// BVHTraversal.cuh:14-134, Intersection.cu:4-36), cut into three resumable steps per lane:
+//   NODE  : pop one wide node, slab-test its 8 children                (node_step_*)
+//   TRI   : one Moller-Trumbore test + closest / any-hit bookkeeping   (tri_step)
+//   SHADE : consume a finished ray (sky / material / sun / scatter / per-sample post) and emit the
+//           lane's next ray, or the next sample of its pixel           (shade_step)
+// A warp repeatedly votes (ballot + popc) for the phase most of its lanes are waiting in and executes
+// only that step, so each step's instructions are issued for many lanes at once instead of for the
+// few that happen to be in that branch (ncu on the monolithic loop: 10.5 of 32 lanes active,
+// profiles/r01a_*). A lane's own sequence of steps -- and its RNG stream -- does not depend on the
+// schedule, so results are identical to render_pixel_flat()/path_radiance() bit for bit.
+//
+// Two node formats feed NODE (chosen per scene, never per node):
+//   Q8  : the builder's 80-byte compressed wide node (drt_types.h WideNode)        -- large scenes
+//   F32 : the same boxes de-quantised once into 256-byte nodes of fp32 planes, laid out
+//         [axis][lo|hi][child] so that "near plane for this ray's sign" is an address offset --
+//         6 FFMA per child instead of 18 convert+select+FFMA (cache-resident scenes are issue-bound)
+#pragma once
+#include "drt_types.h"
+#include "drt_rng.cuh"
+#include "drt_trace.cuh"
+#include "drt_shade.cuh"
+
+namespace drt {
+
+enum { PH_NODE = 0, PH_TRI = 1, PH_SHADE = 2, PH_DONE = 3 };
+enum { NODE_FMT_Q8 = 0, NODE_FMT_F32 = 1 };
+
+#define DRT_F32NODE_F4 16 // float4 per expanded node (256 bytes)
+
+// Expanded node, 16 x float4:
+//   [0]      u4 : child_base, tri_base, imask, 0
+//   [1..2]   u4 : hit contribution of child 0..7 for octant 0: inner slot s -> 1 << (24+s); leaf -> unary << offset; empty -> 0
+//   [3+4a+2s+h] : plane of axis a, side s (0 = lo, 1 = hi), children 4h..4h+3
+//   [15]        : unused
+DRT_HD void expand_wide_node(const WideNode& n, drt_f4* out)
+{
+	drt_u4 h;
+	h.x = n.child_base; h.y = n.tri_base; h.z = n.imask; h.w = 0u;
+	uint32_t contrib[8];
+	float plane[3][2][8];
+	const float p[3] = { n.px, n.py, n.pz };
+	const float sc[3] = { as_float((uint32_t)n.ex << 23), as_float((uint32_t)n.ey << 23), as_float((uint32_t)n.ez << 23) };
+	const uint8_t* q[3][2] = { { n.qlox, n.qhix }, { n.qloy, n.qhiy }, { n.qloz, n.qhiz } };
+	for (int i = 0; i < 8; i++) {
+		const uint32_t mt = n.meta[i];
+		const bool inner = ((mt & (mt << 1)) & 0x10u) != 0u;
+		contrib[i] = mt == 0u ? 0u : (inner ? (1u << (mt & 31u)) : ((mt >> 5) << (mt & 31u)));
+		for (int a = 0; a < 3; a++)
+			for (int s = 0; s < 2; s++)
+				plane[a][s][i] = mt == 0u ? 0.f : p[a] + (float)q[a][s][i] * sc[a]; // exact: q * 2^e, then one rounding (outward-checked below)
+	}
+	// the builder verified base + q*scale brackets the child box in fp32 with this very expression (drt_build.cuh collapse_node)
+	drt_u4* o = (drt_u4*)out;
+	o[0] = h;
+	drt_u4 c0, c1;
+	c0.x = contrib[0]; c0.y = contrib[1]; c0.z = contrib[2]; c0.w = contrib[3];
+	c1.x = contrib[4]; c1.y = contrib[5]; c1.z = contrib[6]; c1.w = contrib[7];
+	o[1] = c0; o[2] = c1;
+	for (int a = 0; a < 3; a++)
+		for (int s = 0; s < 2; s++)
+			for (int hh = 0; hh < 2; hh++) {
+				drt_f4 v;
+				v.x = plane[a][s][4 * hh]; v.y = plane[a][s][4 * hh + 1]; v.z = plane[a][s][4 * hh + 2]; v.w = plane[a][s][4 * hh + 3];
+				out[3 + 4 * a + 2 * s + hh] = v;
+			}
+	drt_f4 z;
+	z.x = z.y = z.z = z.w = 0.f;
+	out[15] = z;
+}
+
+DRT_HD float fast_rcp(float x)
+{
+#if defined(__CUDA_ARCH__)
+	float r;
+	asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); // box tests carry 1e-6 relative slack; MUFU.RCP is within 1 ulp
+	return r;
+#else
+	return 1.0f / x;
+#endif
+}
+
+// Per-ray constants of the conservative slab test. t_near = plane*idn + bn, t_far = plane*idf + bf with
+// idn = id*(1-1e-6), idf = id*(1+1e-6) and the biases pushed outward by a few ulp of |o*id| (the
+// rounding error of the fused form is absolute in that magnitude, not relative to t).
+struct RayBox {
+	float idnx, idny, idnz, bnx, bny, bnz;
+	float idfx, idfy, idfz, bfx, bfy, bfz;
+	uint32_t oct_inv;
+};
+
+DRT_HD void ray_box_setup(V3 o, V3 d, RayBox& R)
+{
+	const float tiny = 1e-20f;
+	const float dx = fabsf(d.x) > tiny ? d.x : (d.x < 0.f ? -tiny : tiny);
+	const float dy = fabsf(d.y) > tiny ? d.y : (d.y < 0.f ? -tiny : tiny);
+	const float dz = fabsf(d.z) > tiny ? d.z : (d.z < 0.f ? -tiny : tiny);
+	const float idx = fast_rcp(dx), idy = fast_rcp(dy), idz = fast_rcp(dz);
+	R.oct_inv = (d.x >= 0.f ? 4u : 0u) | (d.y >= 0.f ? 2u : 0u) | (d.z >= 0.f ? 1u : 0u);
+	const float kn = 0.999999f, kf = 1.000001f, ka = 4.8e-7f;
+	R.idnx = idx * kn; R.idny = idy * kn; R.idnz = idz * kn;
+	R.idfx = idx * kf; R.idfy = idy * kf; R.idfz = idz * kf;
+	const float ex = fabsf(o.x * idx) * ka, ey = fabsf(o.y * idy) * ka, ez = fabsf(o.z * idz) * ka;
+	R.bnx = -(o.x * R.idnx) - ex; R.bny = -(o.y * R.idny) - ey; R.bnz = -(o.z * R.idnz) - ez;
+	R.bfx = -(o.x * R.idfx) + ex; R.bfy = -(o.y * R.idfy) + ey; R.bfz = -(o.z * R.idfz) + ez;
+}
+
+// Traversal state of one lane between steps.
+struct LaneTrav {
+	uint32_t ng_base, ng_bits;   // current node group: child_base | (hit inner slots << 24 | imask)
+	uint32_t tri_base, tri_bits; // pending triangles of the last node
+	int sp;
+	Hit hit;
+	uint32_t best_id;
+};
+
+#ifndef DRT_PSTACK
+#define DRT_PSTACK 32
+#endif
+
+struct LaneStack {
+	uint32_t x[DRT_PSTACK], y[DRT_PSTACK];
+};
+
+DRT_HD void trav_begin(LaneTrav& L, float tmax)
+{
+	L.ng_base = 0u; L.ng_bits = 0x80000000u; // root: one pending inner slot, imask 0 -> relative index 0
+	L.tri_base = 0u; L.tri_bits = 0u;
+	L.sp = 0;
+	L.hit.prim = -1; L.hit.t = tmax; L.hit.u = 0.f; L.hit.v = 0.f;
+	L.best_id = 0xffffffffu;
+}
+
+// Phase of a lane after a NODE or TRI step (pops the stack when the current group is exhausted).
+DRT_HD int trav_advance(LaneTrav& L, LaneStack& S)
+{
+	if (L.tri_bits != 0u) return PH_TRI;
+	if (L.ng_bits > 0x00ffffffu) return PH_NODE;
+	for (;;) {
+		if (L.sp == 0) return PH_SHADE;
+		--L.sp;
+		if (L.sp < DRT_PSTACK) break; // entries beyond the stack were dropped (counted via max_stack)
+	}
+	L.ng_base = S.x[L.sp]; L.ng_bits = S.y[L.sp];
+	return PH_NODE;
+}
+
+// Picks the nearest pending inner child of the current group (octant order) and returns its node index.
+template <bool STATS>
+DRT_HD uint32_t trav_pop_child(LaneTrav& L, LaneStack& S, uint32_t oct_inv, TraceStats* st)
+{
+	const int bit = hi_bit(L.ng_bits);
+	L.ng_bits &= ~(1u << bit);
+	const uint32_t slot = (uint32_t)(bit - 24) ^ oct_inv;
+	const uint32_t rel = (uint32_t)pop_count(L.ng_bits & 0xffu & ((1u << slot) - 1u));
+	const uint32_t node_index = L.ng_base + rel;
+	if (L.ng_bits > 0x00ffffffu) {
+		if (L.sp < DRT_PSTACK) { S.x[L.sp] = L.ng_base; S.y[L.sp] = L.ng_bits; }
+		++L.sp;
+		if (STATS && st && (uint32_t)L.sp > st->max_stack) st->max_stack = (uint32_t)L.sp;
+	}
+	if (STATS && st) st->nodes++;
+	return node_index;
+}
+
+// bits 24..31 of `m` hold child-slot hits in slot order; move bit s to bit s ^ oct_inv
+DRT_HD uint32_t permute_slots(uint32_t m, uint32_t oct_inv)
+{
+	uint32_t b = m >> 24;
+	if (oct_inv & 1u) b = ((b & 0x55u) << 1) | ((b >> 1) & 0x55u);
+	if (oct_inv & 2u) b = ((b & 0x33u) << 2) | ((b >> 2) & 0x33u);
+	if (oct_inv & 4u) b = ((b & 0x0fu) << 4) | (b >> 4);
+	return (m & 0x00ffffffu) | (b << 24);
+}
+
+#define DRT_F32_CHILD(I, NX, NY, NZ, FX, FY, FZ, C)                                                  \
+	{                                                                                                \
+		const float tn = fmaxf(fmax3(fmaf(NX, R.idnx, R.bnx), fmaf(NY, R.idny, R.bny), fmaf(NZ, R.idnz, R.bnz)), 0.f); \
+		const float tf = fminf(fmin3(fmaf(FX, R.idfx, R.bfx), fmaf(FY, R.idfy, R.bfy), fmaf(FZ, R.idfz, R.bfz)), tlim); \
+		if (tn <= tf) hitmask |= (C);                                                                \
+	}
+
+// NODE step on expanded nodes. `nodes` may point to global or shared memory.
+template <bool STATS>
+DRT_HD void node_step_f32(const drt_f4* nodes, LaneTrav& L, LaneStack& S, const RayBox& R, TraceStats* st)
+{
+	const uint32_t node_index = trav_pop_child<STATS>(L, S, R.oct_inv, st);
+	const drt_f4* np = nodes + (size_t)DRT_F32NODE_F4 * node_index;
+	const drt_u4* nu = (const drt_u4*)np;
+	const drt_u4 h = ld_u4(nu);
+	const float tlim = L.hit.t;
+	// near side of axis a: lo if the ray travels towards + (oct_inv bit set), else hi
+	const int sx = (R.oct_inv & 4u) ? 0 : 2, sy = (R.oct_inv & 2u) ? 0 : 2, sz = (R.oct_inv & 1u) ? 0 : 2;
+	const drt_f4* px = np + 3, * py = np + 7, * pz = np + 11;
+	uint32_t hitmask = 0u;
+	{
+		const drt_u4 c = ld_u4(nu + 1);
+		const drt_f4 nx = ld_f4(px + sx), ny = ld_f4(py + sy), nz = ld_f4(pz + sz);
+		const drt_f4 fx = ld_f4(px + (2 - sx)), fy = ld_f4(py + (2 - sy)), fz = ld_f4(pz + (2 - sz));
+		DRT_F32_CHILD(0, nx.x, ny.x, nz.x, fx.x, fy.x, fz.x, c.x)
+		DRT_F32_CHILD(1, nx.y, ny.y, nz.y, fx.y, fy.y, fz.y, c.y)
+		DRT_F32_CHILD(2, nx.z, ny.z, nz.z, fx.z, fy.z, fz.z, c.z)
+		DRT_F32_CHILD(3, nx.w, ny.w, nz.w, fx.w, fy.w, fz.w, c.w)
+	}
+	{
+		const drt_u4 c = ld_u4(nu + 2);
+		const drt_f4 nx = ld_f4(px + sx + 1), ny = ld_f4(py + sy + 1), nz = ld_f4(pz + sz + 1);
+		const drt_f4 fx = ld_f4(px + (2 - sx) + 1), fy = ld_f4(py + (2 - sy) + 1), fz = ld_f4(pz + (2 - sz) + 1);
+		DRT_F32_CHILD(4, nx.x, ny.x, nz.x, fx.x, fy.x, fz.x, c.x)
+		DRT_F32_CHILD(5, nx.y, ny.y, nz.y, fx.y, fy.y, fz.y, c.y)
+		DRT_F32_CHILD(6, nx.z, ny.z, nz.z, fx.z, fy.z, fz.z, c.z)
+		DRT_F32_CHILD(7, nx.w, ny.w, nz.w, fx.w, fy.w, fz.w, c.w)
+	}
+	hitmask = permute_slots(hitmask, R.oct_inv);
+	L.ng_base = h.x;
+	L.ng_bits = (hitmask & 0xff000000u) | (h.z & 0xffu);
+	L.tri_base = h.y;
+	L.tri_bits = hitmask & 0x00ffffffu;
+}
+
+// NODE step on the builder's compressed nodes (same box arithmetic as trace_ray_mode, drt_trace.cuh).
+template <bool STATS>
+DRT_HD void node_step_q8(const drt_u4* nodes, LaneTrav& L, LaneStack& S, const RayBox& R, TraceStats* st)
+{
+	const uint32_t node_index = trav_pop_child<STATS>(L, S, R.oct_inv, st);
+	const drt_u4* np = nodes + 5 * (size_t)node_index;
+	const drt_u4 n0 = ld_u4(np), n1 = ld_u4(np + 1), n2 = ld_u4(np + 2), n3 = ld_u4(np + 3), n4 = ld_u4(np + 4);
+	const float px = as_float(n0.x), py = as_float(n0.y), pz = as_float(n0.z);
+	const float ex = as_float((n0.w & 0xffu) << 23), ey = as_float(((n0.w >> 8) & 0xffu) << 23), ez = as_float(((n0.w >> 16) & 0xffu) << 23);
+	const uint32_t imask = n0.w >> 24;
+	// t = q * (scale*id) + (p*id + b): scale is a power of two, so q*scale*id carries one rounding
+	const float snx = ex * R.idnx, sny = ey * R.idny, snz = ez * R.idnz;
+	const float sfx = ex * R.idfx, sfy = ey * R.idfy, sfz = ez * R.idfz;
+	const float ka = 2.4e-7f;
+	const float enx = (fabsf(px * R.idnx) + 255.f * fabsf(snx)) * ka, eny = (fabsf(py * R.idny) + 255.f * fabsf(sny)) * ka, enz = (fabsf(pz * R.idnz) + 255.f * fabsf(snz)) * ka;
+	const float bnx = fmaf(px, R.idnx, R.bnx) - enx, bny = fmaf(py, R.idny, R.bny) - eny, bnz = fmaf(pz, R.idnz, R.bnz) - enz;
+	const float bfx = fmaf(px, R.idfx, R.bfx) + enx, bfy = fmaf(py, R.idfy, R.bfy) + eny, bfz = fmaf(pz, R.idfz, R.bfz) + enz;
+	const bool posx = (R.oct_inv & 4u) != 0u, posy = (R.oct_inv & 2u) != 0u, posz = (R.oct_inv & 1u) != 0u;
+	// near / far plane words per axis, selected once per node by the ray's sign
+	const uint32_t qnx[2] = { posx ? n2.x : n3.z, posx ? n2.y : n3.w }, qfx[2] = { posx ? n3.z : n2.x, posx ? n3.w : n2.y };
+	const uint32_t qny[2] = { posy ? n2.z : n4.x, posy ? n2.w : n4.y }, qfy[2] = { posy ? n4.x : n2.z, posy ? n4.y : n2.w };
+	const uint32_t qnz[2] = { posz ? n3.x : n4.z, posz ? n3.y : n4.w }, qfz[2] = { posz ? n4.z : n3.x, posz ? n4.w : n3.y };
+	const uint32_t meta[2] = { n1.z, n1.w };
+	const float tlim = L.hit.t;
+	uint32_t hitmask = 0u;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+	for (int i = 0; i < 8; i++) {
+		const int w = i >> 2, sh = (i & 3) * 8;
+		const uint32_t mt = (meta[w] >> sh) & 0xffu;
+		const float t0x = fmaf((float)((qnx[w] >> sh) & 0xffu), snx, bnx), t1x = fmaf((float)((qfx[w] >> sh) & 0xffu), sfx, bfx);
+		const float t0y = fmaf((float)((qny[w] >> sh) & 0xffu), sny, bny), t1y = fmaf((float)((qfy[w] >> sh) & 0xffu), sfy, bfy);
+		const float t0z = fmaf((float)((qnz[w] >> sh) & 0xffu), snz, bnz), t1z = fmaf((float)((qfz[w] >> sh) & 0xffu), sfz, bfz);
+		const float tn = fmaxf(fmax3(t0x, t0y, t0z), 0.f);
+		const float tf = fminf(fmin3(t1x, t1y, t1z), tlim);
+		if (mt != 0u && tn <= tf) {
+			const bool inner = ((mt & (mt << 1)) & 0x10u) != 0u;
+			hitmask |= (inner ? 1u : (mt >> 5)) << (mt & 31u);
+		}
+	}
+	hitmask = permute_slots(hitmask, R.oct_inv);
+	L.ng_base = n1.x;
+	L.ng_bits = (hitmask & 0xff000000u) | imask;
+	L.tri_base = n1.y;
+	L.tri_bits = hitmask & 0x00ffffffu;
+}
+
+// TRI step: tests the lowest pending triangle. Returns true when an any-hit ray is finished (occluded).
+template <bool STRICT, bool STATS>
+DRT_HD bool tri_step(const SceneView& sc, const drt_f4* tris, LaneTrav& L, V3 o, V3 d, bool anyhit, TraceStats* st)
+{
+	typedef M<STRICT> m;
+	const int k = lo_bit(L.tri_bits);
+	L.tri_bits &= L.tri_bits - 1u;
+	const int slot = (int)(L.tri_base + (uint32_t)k);
+	const drt_f4* tp = tris + 3 * (size_t)slot;
+	const drt_f4 r0 = ld_f4(tp), r1 = ld_f4(tp + 1), r2 = ld_f4(tp + 2);
+	if (STATS && st) st->tris++;
+	const V3 v0 = mk3(r0.x, r0.y, r0.z), e1 = mk3(r1.x, r1.y, r1.z), e2 = mk3(r2.x, r2.y, r2.z);
+	// Intersection.cu:8-33, the reference's operation order
+	const V3 pvec = m::cross(d, e2);
+	const float det = m::dot(e1, pvec);
+	if (det > -DRT_TRIANGLE_EPSILON && det < DRT_TRIANGLE_EPSILON) return false;
+	const float inv_det = m::div(1.0f, det);
+	const V3 tvec = m::sub3(o, v0);
+	const float u = m::mul(inv_det, m::dot(tvec, pvec));
+	if (u < 0.0f || u > 1.0f) return false;
+	const V3 qvec = m::cross(tvec, e1);
+	const float v = m::mul(inv_det, m::dot(d, qvec));
+	if (v < 0.0f || m::add(u, v) > 1.0f) return false;
+	const float t = m::mul(inv_det, m::dot(e2, qvec));
+	if (!(t > DRT_TRIANGLE_EPSILON)) return false;
+	const uint32_t matw = as_uint(r1.w);
+	if (anyhit) {
+		if ((matw & 0x80000000u) && !alpha_accept<STRICT>(sc, slot, matw & 0x7fffffffu, u, v, st)) return false;
+		L.hit.prim = slot; L.hit.t = t; L.hit.u = u; L.hit.v = v;
+		return true;
+	}
+	const uint32_t id = as_uint(r0.w);
+	if (!(t < L.hit.t)) {
+		if (!(t == L.hit.t) || L.hit.prim < 0) return false;
+		if (st) st->ties++;
+		if (!(id < L.best_id)) return false;
+	}
+	if ((matw & 0x80000000u) && !alpha_accept<STRICT>(sc, slot, matw & 0x7fffffffu, u, v, st)) return false;
+	L.hit.prim = slot; L.hit.t = t; L.hit.u = u; L.hit.v = v;
+	L.best_id = id;
+	return false;
+}
+
+// Path state of one lane between steps (everything RayGen keeps in locals across its bounce loop).
+struct LanePath {
+	V3 o, d;              // current ray
+	V3 light, throughput;
+	V3 fn;                // face-forwarded normal of the last hit (needed again after the sun shadow ray)
+	V3 acc;               // running per-pixel sum (RenderKernel.cu:29)
+	uint32_t seed;
+	uint32_t k;           // sample of this launch the lane is working on
+	int bounce;
+	bool shadow;          // current ray is the sun shadow ray (RayTest) of the last hit
+};
+
+template <bool STRICT>
+DRT_HD void path_begin_sample(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, LanePath& S)
+{
+	S.light = mk3(0.f, 0.f, 0.f); S.throughput = mk3(1.f, 1.f, 1.f);
+	S.bounce = 0; S.shadow = false;
+	S.seed = (x + y * (uint32_t)P.width) * (P.frame_first + S.k * P.frame_stride); // RayGen.cuh:74-75
+	const RayOD r = camera_get_ray<STRICT>(P.cam, x, y, (uint32_t)P.width, (uint32_t)P.height, S.seed, rtl);
+	S.o = r.o; S.d = r.d;
+}
+
+// SHADE step: consumes the finished ray of this lane. Returns false when the lane has no more work
+// (all samples of its pixel are accumulated); otherwise S.o / S.d hold the next ray to trace.
+// Block for block this is the body of render_pixel_flat() (drt_shade.cuh), i.e. RayGen.cuh:88-169.
+template <bool STRICT, bool STATS>
+DRT_HD bool shade_step(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, const Hit& hit, LanePath& S,
+	PathCounters& pc, TraceStats* st)
+{
+	typedef M<STRICT> m;
+	const SceneView& sc = P.scene;
+	const ShadeParams& SP = P.shade;
+	const bool found = hit.prim >= 0;
+	bool path_done = false, scatter = false;
+	if (S.shadow) {
+		pc.shadow++;
+		if (!found) S.light = m::add3(S.light, m::mul3(SP.suncol, S.throughput)); // RayGen.cuh:126-127
+		S.shadow = false;
+		scatter = true;
+	}
+	else {
+		pc.closest++;
+		S.seed += (uint32_t)S.bounce; // RayGen.cuh:91
+		if (!found) {
+			const V3 sky = sky_model<STRICT>(S.d, SP.sky_color);
+			S.light = m::add3(S.light, m::scale(m::mul3(sky, S.throughput), SP.sky_intensity));
+			path_done = true;
+		}
+		else {
+			const drt_f4 r1 = ld_f4(sc.tris + 3 * (size_t)hit.prim + 1);
+			const uint32_t mat = as_uint(r1.w) & 0x7fffffffu;
+			const drt_f4 mrec = ld_f4(sc.materials + mat);
+			const int tex = (int)as_uint(mrec.w);
+			if (tex < 0) S.throughput = m::mul3(S.throughput, mk3(mrec.x, mrec.y, mrec.z));
+			else {
+				const V2 tuv = interp_uv<STRICT>(sc, hit.prim, hit.u, hit.v);
+				S.throughput = m::mul3(S.throughput, texture_get_pixel<STRICT>(sc, tex, tuv, st));
+			}
+			const drt_f4 s0 = ld_f4(sc.shade + 3 * (size_t)hit.prim);
+			V3 fn = mk3(s0.x, s0.y, s0.z);
+			const V3 pos = m::add3(S.o, m::scale(S.d, hit.t));
+			if (m::dot(fn, m::normalize(S.d)) > 0.f) fn = m::scale(fn, -1.f); // ClosestHit.cuh:17-25
+			S.fn = fn;
+			S.o = m::add3(pos, m::scale(fn, 0.001f));                          // RayGen.cuh:121
+			if (SP.enable_sunlight) {
+				S.d = m::add3(SP.sunpos, m::scale(random_unit_vec3<STRICT>(S.seed, rtl), 1.5f)); // RayGen.cuh:124-125
+				S.shadow = true;
+			}
+			else scatter = true;
+		}
+	}
+	if (scatter) {
+		S.d = m::add3(S.fn, random_unit_sphere_vec3<STRICT>(S.seed, rtl)); // RayGen.cuh:133-134
+		S.bounce++;
+		if (S.bounce > SP.bounce_limit) path_done = true;
+	}
+	if (path_done) {
+		S.acc = m::add3(S.acc, post_process<STRICT>(P, S.light));
+		S.k++;
+		if (S.k >= P.n_samples) return false;
+		path_begin_sample<STRICT>(P, x, y, rtl, S);
+	}
+	return true;
+}
+
+// One lane, serial schedule: the CPU logic tests (tests/hostemu) drive the very same steps with it.
+template <bool STRICT, bool STATS, int FMT>
+DRT_HD V3 render_pixel_steps(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, V3 acc, PathCounters& pc, TraceStats* st)
+{
+	if (P.n_samples == 0) return acc;
+	LanePath S;
+	LaneTrav L;
+	LaneStack K;
+	RayBox R;
+	S.acc = acc; S.k = 0; S.fn = mk3(0.f, 0.f, 0.f);
+	path_begin_sample<STRICT>(P, x, y, rtl, S);
+	ray_box_setup(S.o, S.d, R);
+	trav_begin(L, FLT_MAX);
+	int phase = P.scene.num_nodes > 0 ? PH_NODE : PH_SHADE;
+	while (phase != PH_DONE) {
+		if (phase == PH_NODE) {
+			if (FMT == NODE_FMT_F32) node_step_f32<STATS>(P.scene.nodes_f32, L, K, R, st);
+			else node_step_q8<STATS>(P.scene.nodes, L, K, R, st);
+			phase = trav_advance(L, K);
+		}
+		else if (phase == PH_TRI) {
+			if (tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)) phase = PH_SHADE;
+			else phase = trav_advance(L, K);
+		}
+		else {
+			if (!shade_step<STRICT, STATS>(P, x, y, rtl, L.hit, S, pc, st)) phase = PH_DONE;
+			else {
+				ray_box_setup(S.o, S.d, R);
+				trav_begin(L, FLT_MAX);
+				phase = P.scene.num_nodes > 0 ? PH_NODE : PH_SHADE;
+			}
+		}
+	}
+	return S.acc;
+}
+
+#if defined(__CUDACC__)
+// Scheduling weights of the vote (launch parameters so that they can be swept without recompiling).
+struct PhasedTuning {
+	int bias_node, bias_tri, bias_shade; // added to the lane count of the phase before the arg-max
+};
+
+// One warp: every lane owns one pixel (valid or not) for all samples of the launch.
+template <bool STRICT, bool STATS, int FMT>
+__device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const PhasedTuning T, uint32_t x, uint32_t y, bool valid,
+	bool rtl, V3 acc, PathCounters& pc, TraceStats* st)
+{
+	LanePath S;
+	LaneTrav L;
+	LaneStack K;
+	RayBox R;
+	S.acc = acc; S.k = 0; S.fn = mk3(0.f, 0.f, 0.f);
+	S.o = mk3(0.f, 0.f, 0.f); S.d = mk3(0.f, 0.f, 1.f);
+	S.light = S.throughput = mk3(0.f, 0.f, 0.f);
+	S.seed = 0; S.bounce = 0; S.shadow = false;
+	int phase = PH_DONE;
+	const int first_phase = P.scene.num_nodes > 0 ? PH_NODE : PH_SHADE;
+	trav_begin(L, FLT_MAX);
+	R.oct_inv = 0u;
+	R.idnx = R.idny = R.idnz = R.bnx = R.bny = R.bnz = R.idfx = R.idfy = R.idfz = R.bfx = R.bfy = R.bfz = 0.f;
+	if (valid && P.n_samples > 0) {
+		path_begin_sample<STRICT>(P, x, y, rtl, S);
+		ray_box_setup(S.o, S.d, R);
+		phase = first_phase;
+	}
+	for (;;) {
+		const unsigned mN = __ballot_sync(0xffffffffu, phase == PH_NODE);
+		const unsigned mT = __ballot_sync(0xffffffffu, phase == PH_TRI);
+		const unsigned mS = __ballot_sync(0xffffffffu, phase == PH_SHADE);
+		if ((mN | mT | mS) == 0u) break;
+		const int cN = mN ? __popc(mN) + T.bias_node : 0, cT = mT ? __popc(mT) + T.bias_tri : 0, cS = mS ? __popc(mS) + T.bias_shade : 0;
+		if (cN >= cT && cN >= cS) {
+			if (phase == PH_NODE) {
+				if (FMT == NODE_FMT_F32) node_step_f32<STATS>(P.scene.nodes_f32, L, K, R, st);
+				else node_step_q8<STATS>(P.scene.nodes, L, K, R, st);
+				phase = trav_advance(L, K);
+			}
+		}
+		else if (cT >= cS) {
+			if (phase == PH_TRI) {
+				if (tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)) phase = PH_SHADE;
+				else phase = trav_advance(L, K);
+			}
+		}
+		else {
+			if (phase == PH_SHADE) {
+				if (!shade_step<STRICT, STATS>(P, x, y, rtl, L.hit, S, pc, st)) phase = PH_DONE;
+				else {
+					ray_box_setup(S.o, S.d, R);
+					trav_begin(L, FLT_MAX);
+					phase = first_phase;
+				}
+			}
+		}
+	}
+	return S.acc;
+}
+#endif
+
+} // namespace drt

@@ -2,6 +2,7 @@
 //
 // HBM layout (everything 16-byte aligned so that every load on the path is one LDG.128):
 //   nodes     : 80-byte compressed 8-wide BVH nodes, 5 x uint4 each            (WideNode)
+//   nodes_f32 : the same nodes de-quantised to 256 bytes of fp32 planes (small scenes only; drt_phased.cuh)
 //   tris      : 48 bytes per triangle in LEAF order, 3 x float4:
 //                 [0] v0.xyz | canonical id (index in load order)
 //                 [1] e1.xyz = v1-v0 | material index (bit 31: albedo texture carries alpha -> any-hit test)
@@ -51,6 +52,7 @@ struct SceneView {
 	const TexDesc* textures;
 	const uint32_t* texels;
 	int32_t num_tris, num_nodes, num_materials, num_textures;
+	const drt_f4* nodes_f32; // expanded 256-byte nodes (drt_phased.cuh) or null: built for cache-resident scenes only
 };
 
 // Camera terms that do not depend on the pixel, evaluated once on the host in the reference's

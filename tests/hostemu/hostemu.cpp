@@ -17,6 +17,7 @@
 #include "../../dustraytracer_b200/csrc/drt_host.h"
 #include "../../dustraytracer_b200/csrc/drt_params.h"
 #include "../../dustraytracer_b200/csrc/drt_build_driver.h"
+#include "../../dustraytracer_b200/csrc/drt_phased.cuh"
 
 using namespace drt;
 
@@ -54,7 +55,7 @@ struct EmuExec : BuildExec {
 struct EmuScene {
 	HostScene host;
 	std::vector<int32_t> mat_flags;
-	std::vector<drt_f4> tri_lo, tri_hi, out_tris, out_shade, materials;
+	std::vector<drt_f4> tri_lo, tri_hi, out_tris, out_shade, materials, nodes_f32;
 	std::vector<int> idx0, idx1, pn0, pn1, bins, wide_src;
 	std::vector<BuildNode> nodes;
 	std::vector<BuildSplit> splits;
@@ -133,6 +134,9 @@ int build(EmuScene* s)
 	v.nodes = (const drt_u4*)s->wide.data();
 	v.tris = s->out_tris.data(); v.shade = s->out_shade.data(); v.materials = s->materials.data();
 	v.textures = s->texdesc.data(); v.texels = s->texels.data();
+	s->nodes_f32.resize((size_t)DRT_F32NODE_F4 * (s->result.wide_nodes > 0 ? s->result.wide_nodes : 1));
+	for (int i = 0; i < s->result.wide_nodes; i++) expand_wide_node(s->wide[i], s->nodes_f32.data() + (size_t)DRT_F32NODE_F4 * i);
+	v.nodes_f32 = s->nodes_f32.data();
 	v.num_tris = n; v.num_nodes = s->result.wide_nodes; v.num_materials = (int)s->materials.size(); v.num_textures = (int)s->texdesc.size();
 	return rc;
 }
@@ -319,6 +323,34 @@ void emu_render_flat(void* h, const drt_camera* cam, const drt_settings* st, int
 		c0 += pc.closest; c1 += pc.shadow;
 	}
 	if (counters) { counters[0] = c0; counters[1] = c1; }
+}
+
+// Same contract as emu_render_flat, through the NODE / TRI / SHADE steps of the phased kernel (serial schedule).
+// fmt: 0 = compressed nodes, 1 = expanded fp32 nodes. counters[2..3] = node visits, tri tests.
+void emu_render_steps(void* h, const drt_camera* cam, const drt_settings* st, int W, int H, unsigned first, unsigned stride,
+	unsigned n, int strict, int rtl, int fmt, float* acc, unsigned long long* counters)
+{
+	EmuScene* s = (EmuScene*)h;
+	RenderParams P = make_params(s, cam, st, W, H);
+	P.frame_first = first; P.frame_stride = stride; P.n_samples = n;
+	unsigned long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : c0, c1, c2, c3)
+	for (int y = 0; y < H; y++) {
+		PathCounters pc;
+		pc.closest = pc.shadow = 0;
+		TraceStats ts;
+		memset(&ts, 0, sizeof(ts));
+		for (int x = 0; x < W; x++) {
+			float* a = acc + 3 * ((size_t)x + (size_t)y * W);
+			V3 in = mk3(a[0], a[1], a[2]), r;
+			const bool rt = rtl != 0;
+			if (strict) r = fmt ? render_pixel_steps<true, true, NODE_FMT_F32>(P, x, y, rt, in, pc, &ts) : render_pixel_steps<true, true, NODE_FMT_Q8>(P, x, y, rt, in, pc, &ts);
+			else r = fmt ? render_pixel_steps<false, true, NODE_FMT_F32>(P, x, y, rt, in, pc, &ts) : render_pixel_steps<false, true, NODE_FMT_Q8>(P, x, y, rt, in, pc, &ts);
+			a[0] = r.x; a[1] = r.y; a[2] = r.z;
+		}
+		c0 += pc.closest; c1 += pc.shadow; c2 += ts.nodes; c3 += ts.tris;
+	}
+	if (counters) { counters[0] = c0; counters[1] = c1; counters[2] = c2; counters[3] = c3; }
 }
 
 void emu_camera_params(const drt_camera* cam, int W, int H, float* out20)

@@ -121,6 +121,11 @@ def test_scene_logic_against_golden(emu, name):
         acc, cnt = emu.render(h, g["camera"], g["settings"], rw, rh, 1, 1, frames, strict=True, rtl=True, flat=flat)
         assert np.array_equal(bits(acc), bits(g["acc"])), "flat=%s" % flat
         assert cnt[0] == int(g["rays"][0]) and cnt[1] == int(g["rays"][1])
+    # the phased kernel's NODE / TRI / SHADE steps (serial schedule), on both node formats
+    for fmt in (0, 1):
+        acc, cnt = emu.render(h, g["camera"], g["settings"], rw, rh, 1, 1, frames, strict=True, rtl=True, steps=fmt)
+        assert np.array_equal(bits(acc), bits(g["acc"])), "steps fmt=%d" % fmt
+        assert cnt[0] == int(g["rays"][0]) and cnt[1] == int(g["rays"][1])
     emu.free(h)
 
 

@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--flags", type=int, default=0)
+    ap.add_argument("--bias", default="0:0:0", help="comma list of node:tri:shade vote biases (phased variants)")
     a = ap.parse_args()
     for name in a.scenes.split(","):
         sun, bounces = CONFIGS.get(name, (1, 2))
@@ -36,7 +37,8 @@ def main():
         st = scene.stats()
         cam = drt.Camera()
         for v in [int(x) for x in a.variants.split(",")]:
-            for b in [int(x) for x in a.blocks.split(",")]:
+            for b, bias in [(int(x), y) for x in a.blocks.split(",") for y in (a.bias.split(",") if v >= 2 else ["0:0:0"])]:
+                os.environ["DRT_SCHED_BIAS"] = bias.replace(":", ",")
                 r = drt.Renderer(flags=a.flags)
                 r.m_RendererSettings = drt.RendererSettings(enable_sunlight=sun, ray_bounce_limit=bounces, max_samples=1 << 30)
                 r.set_tuning(v, b)
@@ -53,7 +55,7 @@ def main():
                         best = (ms, rays, c)
                 ms, rays, c = best
                 out = {"scene": name, "tris": st["triangles"], "wide_nodes": st["wide_nodes"], "build_ms": round(st["build_ms"], 3),
-                       "variant": v, "block": b, "spp": a.spp, "ms": round(ms, 3), "Mrays_s": round(rays / ms / 1e3, 1),
+                       "variant": v, "block": b, "bias": bias, "spp": a.spp, "ms": round(ms, 3), "Mrays_s": round(rays / ms / 1e3, 1),
                        "Msamples_s": round(a.width * a.height * a.spp / ms / 1e3, 1), "rays": rays}
                 if a.flags & 4:
                     out.update({"nodes_per_ray": round(c["node_visits"] / rays, 3), "tris_per_ray": round(c["tri_tests"] / rays, 3),
