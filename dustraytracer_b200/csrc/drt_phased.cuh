@@ -496,4 +496,239 @@ __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const Ph
 }
 #endif
 
+
+// =============================================================================================
+// Five-step decomposition (NODE, TRI, HIT, UVEC, END) with overlapping NODE/TRI eligibility.
+//   * A lane in traversal may hold BOTH pending triangles and pending child nodes. It can take part in a
+//     NODE step (its pending triangles are parked on the traversal stack as a triangle group, the way
+//     compressed-wide-BVH traversal postpones leaves) or in a TRI step, whichever the warp runs next.
+//   * The per-ray shading of RayGen.cuh:88-169 is cut where its control flow forks, so that the
+//     expensive pieces run for lanes that all need them:
+//       HIT  : closest-hit ray finished  -> sky on a miss, else material / normal / next origin
+//       UVEC : one random_unit_vec3 draw -> the sun shadow direction, or ONE try of the scatter rejection
+//              loop (Random.cu:50-58; a rejected try leaves the lane in UVEC for the next vote)
+//       END  : sample finished           -> per-sample post-process, accumulate, next camera ray
+// =============================================================================================
+enum { ST_NODE = 0, ST_TRI = 1, ST_HIT = 2, ST_UVEC = 3, ST_END = 4, ST_COUNT = 5 };
+enum { LP_TRAV = 0, LP_HIT = 1, LP_UVEC = 2, LP_END = 3, LP_DONE = 4 };
+enum { UV_SHADOWGEN = 0, UV_SCATTER = 1 };
+
+struct LanePath5 {
+	V3 o, d;
+	V3 light, throughput;
+	V3 fn;
+	V3 acc;
+	uint32_t seed;
+	uint32_t k;
+	int bounce;
+	bool shadow;   // the ray being traced is a sun shadow ray
+	bool sunflag;  // a shadow ray just finished: UVEC applies its result before drawing
+	int uvmode;
+};
+
+// After a NODE or TRI step: true while the lane still has traversal work (pops the stack if needed).
+DRT_HD bool trav_settle(LaneTrav& L, LaneStack& S)
+{
+	if (L.tri_bits != 0u || L.ng_bits > 0x00ffffffu) return true;
+	for (;;) {
+		if (L.sp == 0) return false;
+		--L.sp;
+		if (L.sp < DRT_PSTACK) break;
+	}
+	const uint32_t x = S.x[L.sp], y = S.y[L.sp];
+	if (y > 0x00ffffffu) { L.ng_base = x; L.ng_bits = y; }
+	else { L.tri_base = x; L.tri_bits = y; }
+	return true;
+}
+
+// Parks the pending triangle group so that the lane can run a NODE step first.
+template <bool STATS>
+DRT_HD void trav_postpone_tris(LaneTrav& L, LaneStack& S, TraceStats* st)
+{
+	if (L.tri_bits == 0u) return;
+	if (L.sp < DRT_PSTACK) { S.x[L.sp] = L.tri_base; S.y[L.sp] = L.tri_bits; }
+	++L.sp;
+	if (STATS && st && (uint32_t)L.sp > st->max_stack) st->max_stack = (uint32_t)L.sp;
+	L.tri_bits = 0u;
+}
+
+template <bool STRICT>
+DRT_HD void path5_begin_sample(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, LanePath5& S)
+{
+	S.light = mk3(0.f, 0.f, 0.f); S.throughput = mk3(1.f, 1.f, 1.f);
+	S.bounce = 0; S.shadow = false; S.sunflag = false;
+	S.seed = (x + y * (uint32_t)P.width) * (P.frame_first + S.k * P.frame_stride);
+	const RayOD r = camera_get_ray<STRICT>(P.cam, x, y, (uint32_t)P.width, (uint32_t)P.height, S.seed, rtl);
+	S.o = r.o; S.d = r.d;
+}
+
+// HIT: a closest-hit ray finished. Returns the lane's next phase (LP_END on a miss, else LP_UVEC).
+template <bool STRICT, bool STATS>
+DRT_HD int hit_step(const RenderParams& P, const Hit& hit, LanePath5& S, PathCounters& pc, TraceStats* st)
+{
+	typedef M<STRICT> m;
+	const SceneView& sc = P.scene;
+	const ShadeParams& SP = P.shade;
+	pc.closest++;
+	S.seed += (uint32_t)S.bounce;
+	if (hit.prim < 0) {
+		const V3 sky = sky_model<STRICT>(S.d, SP.sky_color);
+		S.light = m::add3(S.light, m::scale(m::mul3(sky, S.throughput), SP.sky_intensity));
+		return LP_END;
+	}
+	const drt_f4 r1 = ld_f4(sc.tris + 3 * (size_t)hit.prim + 1);
+	const uint32_t mat = as_uint(r1.w) & 0x7fffffffu;
+	const drt_f4 mrec = ld_f4(sc.materials + mat);
+	const int tex = (int)as_uint(mrec.w);
+	if (tex < 0) S.throughput = m::mul3(S.throughput, mk3(mrec.x, mrec.y, mrec.z));
+	else {
+		const V2 tuv = interp_uv<STRICT>(sc, hit.prim, hit.u, hit.v);
+		S.throughput = m::mul3(S.throughput, texture_get_pixel<STRICT>(sc, tex, tuv, st));
+	}
+	const drt_f4 s0 = ld_f4(sc.shade + 3 * (size_t)hit.prim);
+	V3 fn = mk3(s0.x, s0.y, s0.z);
+	const V3 pos = m::add3(S.o, m::scale(S.d, hit.t));
+	if (m::dot(fn, m::normalize(S.d)) > 0.f) fn = m::scale(fn, -1.f);
+	S.fn = fn;
+	S.o = m::add3(pos, m::scale(fn, 0.001f));
+	S.uvmode = SP.enable_sunlight ? UV_SHADOWGEN : UV_SCATTER;
+	return LP_UVEC;
+}
+
+// UVEC: one draw. Returns LP_TRAV (S.o/S.d hold a new ray), LP_UVEC (rejected try) or LP_END (bounce limit).
+template <bool STRICT>
+DRT_HD int uvec_step(const RenderParams& P, bool rtl, bool shadow_found, LanePath5& S, PathCounters& pc)
+{
+	typedef M<STRICT> m;
+	const ShadeParams& SP = P.shade;
+	if (S.sunflag) {
+		pc.shadow++;
+		if (!shadow_found) S.light = m::add3(S.light, m::mul3(SP.suncol, S.throughput));
+		S.sunflag = false; S.shadow = false;
+		S.uvmode = UV_SCATTER;
+	}
+	const V3 v = random_unit_vec3<STRICT>(S.seed, rtl);
+	if (S.uvmode == UV_SHADOWGEN) {
+		S.d = m::add3(SP.sunpos, m::scale(v, 1.5f));
+		S.shadow = true;
+		return LP_TRAV;
+	}
+	const float len = m::length(v);
+	if (!(m::mul(len, len) < 1.f)) return LP_UVEC;
+	S.d = m::add3(S.fn, v);
+	S.bounce++;
+	return S.bounce > SP.bounce_limit ? LP_END : LP_TRAV;
+}
+
+// END: the sample is complete. Returns LP_DONE or LP_TRAV (next sample's camera ray in S.o/S.d).
+template <bool STRICT>
+DRT_HD int end_step(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, LanePath5& S)
+{
+	typedef M<STRICT> m;
+	S.acc = m::add3(S.acc, post_process<STRICT>(P, S.light));
+	S.k++;
+	if (S.k >= P.n_samples) return LP_DONE;
+	path5_begin_sample<STRICT>(P, x, y, rtl, S);
+	return LP_TRAV;
+}
+
+// Phase of a lane whose traversal just ran out of work.
+DRT_HD int trav_finished_phase(LanePath5& S)
+{
+	if (S.shadow) { S.sunflag = true; return LP_UVEC; }
+	return LP_HIT;
+}
+
+// All state of one lane for the five-step kernels.
+struct Lane5 {
+	LanePath5 S;
+	LaneTrav L;
+	LaneStack K;
+	RayBox R;
+	int phase;
+};
+
+template <bool STRICT>
+DRT_HD void lane5_init(const RenderParams& P, uint32_t x, uint32_t y, bool valid, bool rtl, V3 acc, Lane5& A)
+{
+	A.S.acc = acc; A.S.k = 0; A.S.fn = mk3(0.f, 0.f, 0.f);
+	A.S.o = mk3(0.f, 0.f, 0.f); A.S.d = mk3(0.f, 0.f, 1.f);
+	A.S.light = A.S.throughput = mk3(0.f, 0.f, 0.f);
+	A.S.seed = 0; A.S.bounce = 0; A.S.shadow = false; A.S.sunflag = false; A.S.uvmode = UV_SCATTER;
+	trav_begin(A.L, FLT_MAX);
+	A.R.oct_inv = 0u;
+	A.R.idnx = A.R.idny = A.R.idnz = A.R.bnx = A.R.bny = A.R.bnz = 0.f;
+	A.R.idfx = A.R.idfy = A.R.idfz = A.R.bfx = A.R.bfy = A.R.bfz = 0.f;
+	A.phase = LP_DONE;
+	if (valid && P.n_samples > 0) {
+		path5_begin_sample<STRICT>(P, x, y, rtl, A.S);
+		ray_box_setup(A.S.o, A.S.d, A.R);
+		A.phase = P.scene.num_nodes > 0 ? LP_TRAV : LP_HIT;
+	}
+}
+
+// A new ray is in S.o / S.d: reset the traversal.
+DRT_HD void lane5_new_ray(const RenderParams& P, Lane5& A)
+{
+	ray_box_setup(A.S.o, A.S.d, A.R);
+	trav_begin(A.L, FLT_MAX);
+	if (P.scene.num_nodes <= 0) A.phase = trav_finished_phase(A.S);
+}
+
+DRT_HD bool lane5_wants(const Lane5& A, int step)
+{
+	switch (step) {
+	case ST_NODE: return A.phase == LP_TRAV && A.L.ng_bits > 0x00ffffffu;
+	case ST_TRI: return A.phase == LP_TRAV && A.L.tri_bits != 0u;
+	case ST_HIT: return A.phase == LP_HIT;
+	case ST_UVEC: return A.phase == LP_UVEC;
+	default: return A.phase == LP_END;
+	}
+}
+
+// Executes `step` for a lane that wants it.
+template <bool STRICT, bool STATS, int FMT>
+DRT_HD void lane5_run(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, int step, Lane5& A, PathCounters& pc, TraceStats* st)
+{
+	if (step == ST_NODE) {
+		trav_postpone_tris<STATS>(A.L, A.K, st);
+		if (FMT == NODE_FMT_F32) node_step_f32<STATS>(P.scene.nodes_f32, A.L, A.K, A.R, st);
+		else node_step_q8<STATS>(P.scene.nodes, A.L, A.K, A.R, st);
+		if (!trav_settle(A.L, A.K)) A.phase = trav_finished_phase(A.S);
+	}
+	else if (step == ST_TRI) {
+		if (tri_step<STRICT, STATS>(P.scene, P.scene.tris, A.L, A.S.o, A.S.d, A.S.shadow, st)) A.phase = trav_finished_phase(A.S);
+		else if (!trav_settle(A.L, A.K)) A.phase = trav_finished_phase(A.S);
+	}
+	else if (step == ST_HIT) {
+		A.phase = hit_step<STRICT, STATS>(P, A.L.hit, A.S, pc, st);
+	}
+	else if (step == ST_UVEC) {
+		A.phase = uvec_step<STRICT>(P, rtl, A.L.hit.prim >= 0, A.S, pc);
+		if (A.phase == LP_TRAV) lane5_new_ray(P, A);
+	}
+	else {
+		A.phase = end_step<STRICT>(P, x, y, rtl, A.S);
+		if (A.phase == LP_TRAV) lane5_new_ray(P, A);
+	}
+}
+
+// One lane, serial schedule (triangles before nodes, like the reference-shaped traversal).
+template <bool STRICT, bool STATS, int FMT>
+DRT_HD V3 render_pixel_steps5(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, V3 acc, PathCounters& pc, TraceStats* st, bool nodes_first)
+{
+	Lane5 A;
+	lane5_init<STRICT>(P, x, y, true, rtl, acc, A);
+	while (A.phase != LP_DONE) {
+		int step;
+		if (A.phase == LP_TRAV) {
+			const bool wn = lane5_wants(A, ST_NODE), wt = lane5_wants(A, ST_TRI);
+			step = (wn && (nodes_first || !wt)) ? ST_NODE : ST_TRI;
+		}
+		else step = A.phase == LP_HIT ? ST_HIT : (A.phase == LP_UVEC ? ST_UVEC : ST_END);
+		lane5_run<STRICT, STATS, FMT>(P, x, y, rtl, step, A, pc, st);
+	}
+	return A.S.acc;
+}
+
 } // namespace drt

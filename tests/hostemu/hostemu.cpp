@@ -353,6 +353,139 @@ void emu_render_steps(void* h, const drt_camera* cam, const drt_settings* st, in
 	if (counters) { counters[0] = c0; counters[1] = c1; counters[2] = c2; counters[3] = c3; }
 }
 
+// Design tool (tools/sched_sim.py): the sequence of phase steps each lane of one 8x4 tile executes, as a
+// string over N (node step), T (triangle step), H (closest-hit processing), U (one random-unit-vector
+// attempt: sun shadow direction or one try of the scatter rejection loop), E (sample end: sky on a miss,
+// post-process, next camera ray). The sequence of a lane does not depend on how a warp schedules it.
+int emu_phase_trace(void* h, const drt_camera* cam, const drt_settings* st, int W, int H, int tile_x, int tile_y,
+	unsigned first, unsigned n, char* out, int cap_per_lane)
+{
+	EmuScene* s = (EmuScene*)h;
+	RenderParams P = make_params(s, cam, st, W, H);
+	P.frame_first = first; P.frame_stride = 1; P.n_samples = n;
+	const bool rtl = false;
+	int longest = 0;
+	for (int lane = 0; lane < 32; lane++) {
+		char* o = out + (size_t)lane * cap_per_lane;
+		int len = 0;
+		const int x = tile_x * 8 + (lane & 7), y = tile_y * 4 + (lane >> 3);
+		o[0] = 0;
+		if (x >= W || y >= H) continue;
+		LanePath S; LaneTrav L; LaneStack K; RayBox R; PathCounters pc; pc.closest = pc.shadow = 0;
+		S.acc = mk3(0, 0, 0); S.k = 0; S.fn = mk3(0, 0, 0);
+		path_begin_sample<false>(P, x, y, rtl, S);
+		ray_box_setup(S.o, S.d, R);
+		trav_begin(L, FLT_MAX);
+		int phase = PH_NODE;
+		while (phase != PH_DONE && len < cap_per_lane - 8) {
+			if (phase == PH_NODE) { o[len++] = 'N'; node_step_q8<false>(P.scene.nodes, L, K, R, nullptr); phase = trav_advance(L, K); }
+			else if (phase == PH_TRI) {
+				o[len++] = 'T';
+				if (tri_step<false, false>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, nullptr)) phase = PH_SHADE; else phase = trav_advance(L, K);
+			}
+			else {
+				const bool was_shadow = S.shadow, found = L.hit.prim >= 0;
+				const unsigned k0 = S.k;
+				uint32_t seed = S.seed;
+				const int bounce0 = S.bounce;
+				int attempts = 0;
+				if (was_shadow || (found && !P.shade.enable_sunlight)) { // count the tries of the scatter rejection loop
+					if (!was_shadow) seed += (uint32_t)bounce0;
+					for (;;) { attempts++; V3 p = random_unit_vec3<false>(seed, rtl); float l = M<false>::length(p); if (l * l < 1.f) break; }
+				}
+				const bool alive = shade_step<false, false>(P, x, y, rtl, L.hit, S, pc, nullptr);
+				if (!was_shadow && found) o[len++] = 'H';
+				if (!was_shadow && found && P.shade.enable_sunlight) o[len++] = 'U';
+				for (int a = 0; a < attempts; a++) o[len++] = 'U';
+				if (S.k != k0 || !alive) o[len++] = 'E';
+				if (!alive) phase = PH_DONE;
+				else { ray_box_setup(S.o, S.d, R); trav_begin(L, FLT_MAX); phase = PH_NODE; }
+			}
+		}
+		o[len] = 0;
+		if (len > longest) longest = len;
+	}
+	return longest;
+}
+
+// Five-step decomposition (drt_phased.cuh), serial schedule; nodes_first exercises triangle postponement.
+void emu_render_steps5(void* h, const drt_camera* cam, const drt_settings* st, int W, int H, unsigned first, unsigned stride,
+	unsigned n, int strict, int rtl, int fmt, int nodes_first, float* acc, unsigned long long* counters)
+{
+	EmuScene* s = (EmuScene*)h;
+	RenderParams P = make_params(s, cam, st, W, H);
+	P.frame_first = first; P.frame_stride = stride; P.n_samples = n;
+	unsigned long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : c0, c1, c2, c3)
+	for (int y = 0; y < H; y++) {
+		PathCounters pc;
+		pc.closest = pc.shadow = 0;
+		TraceStats ts;
+		memset(&ts, 0, sizeof(ts));
+		for (int x = 0; x < W; x++) {
+			float* a = acc + 3 * ((size_t)x + (size_t)y * W);
+			V3 in = mk3(a[0], a[1], a[2]), r;
+			const bool rt = rtl != 0, nf = nodes_first != 0;
+			if (strict) r = fmt ? render_pixel_steps5<true, true, NODE_FMT_F32>(P, x, y, rt, in, pc, &ts, nf) : render_pixel_steps5<true, true, NODE_FMT_Q8>(P, x, y, rt, in, pc, &ts, nf);
+			else r = fmt ? render_pixel_steps5<false, true, NODE_FMT_F32>(P, x, y, rt, in, pc, &ts, nf) : render_pixel_steps5<false, true, NODE_FMT_Q8>(P, x, y, rt, in, pc, &ts, nf);
+			a[0] = r.x; a[1] = r.y; a[2] = r.z;
+		}
+		c0 += pc.closest; c1 += pc.shadow; c2 += ts.nodes; c3 += ts.tris;
+	}
+	if (counters) { counters[0] = c0; counters[1] = c1; counters[2] = c2; counters[3] = c3; }
+}
+
+// Design tool (tools/sched_sim.py): emulates ONE WARP of the five-step kernel over an 8x4 tile with the vote
+// score_s = lanes wanting s * weight[s] (+ sticky bonus for the step that ran last), executes the winner for
+// every lane that wants it, and reports per step: executions, lane-steps. overlap = 0 makes a lane with
+// pending triangles ineligible for NODE (the exclusive schedule of the three-phase kernel).
+// out[0..4] = executions, out[5..9] = lane-steps, out[10] = rays, out[11] = node visits
+void emu_warp_sim(void* h, const drt_camera* cam, const drt_settings* st, int W, int H, int tile_x, int tile_y, unsigned first,
+	unsigned n, const float* weight, float sticky, int overlap, int pool, unsigned long long* out)
+{
+	if (pool < 1) pool = 1;
+	const int NL = 32 * pool; // contexts owned by the warp: `pool` horizontally adjacent tiles
+	EmuScene* s = (EmuScene*)h;
+	RenderParams P = make_params(s, cam, st, W, H);
+	P.frame_first = first; P.frame_stride = 1; P.n_samples = n;
+	std::vector<Lane5> lanes(NL);
+	PathCounters pc; pc.closest = pc.shadow = 0;
+	TraceStats ts; memset(&ts, 0, sizeof(ts));
+	auto px = [&](int l) { return (tile_x + l / 32) * 8 + (l & 7); };
+	auto py = [&](int l) { return tile_y * 4 + ((l & 31) >> 3); };
+	for (int l = 0; l < NL; l++) lane5_init<false>(P, px(l), py(l), px(l) < W && py(l) < H, false, mk3(0, 0, 0), lanes[l]);
+	int last = -1;
+	for (;;) {
+		int cnt[ST_COUNT] = { 0, 0, 0, 0, 0 };
+		for (int l = 0; l < NL; l++)
+			for (int k = 0; k < ST_COUNT; k++) {
+				bool w = lane5_wants(lanes[l], k);
+				if (k == ST_NODE && !overlap && lanes[l].L.tri_bits != 0u) w = false;
+				if (w) cnt[k]++;
+			}
+		int best = -1; float bs = 0.f;
+		for (int k = 0; k < ST_COUNT; k++) {
+			if (!cnt[k]) continue;
+			float sc = (cnt[k] > 32 ? 32 : cnt[k]) * weight[k] + (k == last ? sticky : 0.f);
+			if (best < 0 || sc > bs) { best = k; bs = sc; }
+		}
+		if (best < 0) break;
+		last = best;
+		out[best]++;
+		int served = 0;
+		for (int l = 0; l < NL && served < 32; l++) {
+			bool w = lane5_wants(lanes[l], best);
+			if (best == ST_NODE && !overlap && lanes[l].L.tri_bits != 0u) w = false;
+			if (!w) continue;
+			out[5 + best]++;
+			served++;
+			lane5_run<false, true, NODE_FMT_Q8>(P, px(l), py(l), false, best, lanes[l], pc, &ts);
+		}
+	}
+	out[10] += pc.closest + pc.shadow;
+	out[11] += ts.nodes;
+}
+
 void emu_camera_params(const drt_camera* cam, int W, int H, float* out20)
 {
 	CameraParams c = make_camera_params(*cam, W, H);

@@ -126,6 +126,11 @@ def test_scene_logic_against_golden(emu, name):
         acc, cnt = emu.render(h, g["camera"], g["settings"], rw, rh, 1, 1, frames, strict=True, rtl=True, steps=fmt)
         assert np.array_equal(bits(acc), bits(g["acc"])), "steps fmt=%d" % fmt
         assert cnt[0] == int(g["rays"][0]) and cnt[1] == int(g["rays"][1])
+    # the five-step decomposition, triangles-first and nodes-first (postponed triangle groups)
+    for fmt, nodes_first in ((0, 0), (1, 1), (0, 1)):
+        acc, cnt = emu.render(h, g["camera"], g["settings"], rw, rh, 1, 1, frames, strict=True, rtl=True, steps5=(fmt, nodes_first))
+        assert np.array_equal(bits(acc), bits(g["acc"])), "steps5 fmt=%d nodes_first=%d" % (fmt, nodes_first)
+        assert cnt[0] == int(g["rays"][0]) and cnt[1] == int(g["rays"][1])
     emu.free(h)
 
 
