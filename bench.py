@@ -121,6 +121,34 @@ def cpu_reference_step(orc, oh, frame, frames=1, threads=0):
     return rays[0] + rays[1], sec
 
 
+def ref_cuda_baseline(frames=8):
+    """The reference's own CUDA path (unmodified sources, nvcc sm_100a, oracle/_ref/libdrt_refcuda*.so) on the same
+    GPU, workload and launch shape as its Renderer (one 8x8-block launch + event pair per sample). Reported beside
+    our number (north_star: >= 10x the reference's CUDA traversal on one B200); None when the libraries did not travel."""
+    import numpy as np
+    import oracles as O
+    out = {}
+    for key, lib in (("O3", "libdrt_refcuda.so"), ("O3_fast_math", "libdrt_refcuda_fast.so")):
+        path = os.path.join(ROOT, "oracle", "_ref", lib)
+        if not os.path.exists(path):
+            continue
+        L = ctypes.CDLL(path)
+        L.refcuda_load.restype = ctypes.c_void_p
+        L.refcuda_render.restype = ctypes.c_double
+        h = L.refcuda_load(SCENE_PATH.encode(), 8, 20)  # editor values: 8 bins, 20-triangle leaves (EditorLayer.cpp:53-54)
+        cam = O.default_camera_bytes()
+        st = O.settings_bytes(sun=WORKLOAD["sun"], bounces=WORKLOAD["bounces"], max_samples=100000)
+        P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+        W, H = WORKLOAD["width"], WORKLOAD["height"]
+        L.refcuda_render(ctypes.c_void_p(h), P(cam), P(st), W, H, 1, 2, None)  # warm-up
+        acc = np.zeros(W * H * 3, np.float32)
+        ms = L.refcuda_render(ctypes.c_void_p(h), P(cam), P(st), W, H, 1, frames, P(acc))
+        out[key] = {"ms_per_sample": ms / frames, "samples_per_s": W * H * frames / (ms * 1e-3), "frames": frames,
+                    "mean_ldr": float(acc.mean() / frames)}
+        L.refcuda_free(ctypes.c_void_p(h))
+    return out or None
+
+
 def run_reference(args, rank):
     if rank != 0:
         return 0
@@ -180,7 +208,7 @@ def run_ours(args, rank, world, local_rank):
     cam = drt.Camera()
     r = drt.Renderer(device=local_rank)
     r.m_RendererSettings = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=WORKLOAD["bounces"], max_samples=1 << 30)
-    r.set_tuning(int(os.environ.get("DRT_VARIANT", "2")), int(os.environ.get("DRT_BLOCK", "0")))
+    r.set_tuning(int(os.environ.get("DRT_VARIANT", "4")), int(os.environ.get("DRT_BLOCK", "0")))
     r.ResizeBuffer(W, H)
     stream = torch.cuda.current_stream(dev)
     r.set_stream(stream.cuda_stream)
@@ -279,6 +307,14 @@ def run_ours(args, rank, world, local_rank):
                "sample": "%d of the 256 samples per pixel (frame indices 1..%d) of the same 1920x1080 frame, %.1f s"
                          % (CPU_SAMPLE_FRAMES, CPU_SAMPLE_FRAMES, csec)}
         value = total_rays / (max_ms * 1e-3) / 1e6
+        try:
+            refcuda = ref_cuda_baseline()
+        except Exception as e:  # measurement aid only
+            refcuda = {"error": str(e)}
+        if refcuda and "error" not in refcuda:
+            rays_per_sample = total_rays / args.steps / world / SPP   # same workload: rays are a property of the frame
+            for v in refcuda.values():
+                v["Mrays_s_at_our_ray_count"] = rays_per_sample / (v["ms_per_sample"] * 1e-3) / 1e6
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": max_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -290,6 +326,7 @@ def run_ours(args, rank, world, local_rank):
                        "build_ms": sstats["build_ms"]},
             "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 152, "d2h_bytes_per_step": W * H * 16},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "reference_cuda_on_this_gpu": refcuda,
             "rays_per_step": total_rays / args.steps, "wall_s_timed_region": t_wall,
         }
         print(json.dumps(line), flush=True)

@@ -91,6 +91,9 @@ def build_oracle(force=False):
     if os.path.isdir("/root/reference/DustRayTracer/src"):
         _run(["make", "-C", odir, "ref"] + (["-B"] if force else []))
         built.append(REF_LIB)
+        # the reference's CUDA path for the GPU box (measurement baseline, ~3 min the first time)
+        _run(["make", "-C", odir, "refcuda"] + (["-B"] if force else []))
+        built += [os.path.join(odir, "_ref", "libdrt_refcuda.so"), os.path.join(odir, "_ref", "libdrt_refcuda_fast.so")]
     return built
 
 

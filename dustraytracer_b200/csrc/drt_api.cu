@@ -117,7 +117,7 @@ struct drt_renderer {
 	uint32_t samples_done = 0;  // samples accumulated by THIS renderer
 	uint32_t first_frame = 1, stride = 1;
 	uint32_t flags = 0;
-	int variant = 2, block_threads = 0;
+	int variant = 4, block_threads = 0;
 	int sched_bias[3] = { 0, 0, 0 };
 	int kernel_launches = 0;
 };
@@ -476,7 +476,7 @@ extern "C" int drt_renderer_set_flags(drt_renderer* r, uint32_t flags)
 extern "C" int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads)
 {
 	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: null renderer");
-	if (variant < 0 || variant > 3 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
+	if (variant < 0 || variant > 6 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
 	r->variant = variant; r->block_threads = block_threads;
 	return DRT_OK;
 }

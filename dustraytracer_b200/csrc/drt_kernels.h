@@ -10,7 +10,7 @@ struct LaunchConfig {
 	bool strict = false;  // DRT_FLAG_STRICT
 	bool rtl = false;     // DRT_FLAG_HOST_ARG_ORDER
 	bool stats = false;   // DRT_FLAG_STATS
-	int variant = 2;      // render kernel variant (see drt_kernels.cu); 2 = default
+	int variant = 4;      // render kernel variant (see drt_kernels.cu); 4 = default
 	int sched_bias[3] = { 0, 0, 0 }; // phased kernels: vote bias of NODE / TRI / SHADE
 	int block_threads = 0; // 0 = variant default
 };

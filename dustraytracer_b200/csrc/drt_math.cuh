@@ -70,19 +70,28 @@ template <bool STRICT> struct M {
 #endif
 		return a - b;
 	}
+	// production mode uses the hardware approximations (MUFU.RCP / MUFU.SQRT, <= 2 ulp), like the reference's
+	// Release build (--use_fast_math, premake5.lua:85); parity mode keeps IEEE round-to-nearest
 	static DRT_HD float div(float a, float b)
 	{
 #if defined(__CUDA_ARCH__)
 		if (STRICT) return __fdiv_rn(a, b);
-#endif
+		return __fdividef(a, b);
+#else
 		return a / b;
+#endif
 	}
 	static DRT_HD float sqrt(float a)
 	{
 #if defined(__CUDA_ARCH__)
 		if (STRICT) return __fsqrt_rn(a);
-#endif
+		float r;
+		// the approximate tonemap quotient can land a few ulp below zero where the exact one is +0: clamp, never NaN
+		asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaxf(a, 0.f)));
+		return r;
+#else
 		return sqrtf(a);
+#endif
 	}
 	// reciprocal square root: host helper_math defines rsqrtf(x) = 1.0f / sqrtf(x) (helper_math.cuh:78-81)
 	static DRT_HD float rsqrt(float a)
@@ -98,8 +107,10 @@ template <bool STRICT> struct M {
 	{
 #if defined(__CUDA_ARCH__)
 		if (STRICT) return __fdiv_rn(1.0f, a);
-#endif
+		return __fdividef(1.0f, a);
+#else
 		return 1.0f / a;
+#endif
 	}
 
 	static DRT_HD V3 add3(V3 a, V3 b) { return mk3(add(a.x, b.x), add(a.y, b.y), add(a.z, b.z)); }

@@ -463,10 +463,10 @@ __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const Ph
 		phase = first_phase;
 	}
 	for (;;) {
-		const unsigned mN = __ballot_sync(0xffffffffu, phase == PH_NODE);
-		const unsigned mT = __ballot_sync(0xffffffffu, phase == PH_TRI);
-		const unsigned mS = __ballot_sync(0xffffffffu, phase == PH_SHADE);
-		if ((mN | mT | mS) == 0u) break;
+		// two ballots over the bits of `phase` (NODE 0, TRI 1, SHADE 2, DONE 3) give the three lane sets
+		const unsigned b0 = __ballot_sync(0xffffffffu, (phase & 1) != 0), b1 = __ballot_sync(0xffffffffu, (phase & 2) != 0);
+		if ((b0 & b1) == 0xffffffffu) break;
+		const unsigned mN = ~(b0 | b1), mT = b0 & ~b1, mS = b1 & ~b0;
 		const int cN = mN ? __popc(mN) + T.bias_node : 0, cT = mT ? __popc(mT) + T.bias_tri : 0, cS = mS ? __popc(mS) + T.bias_shade : 0;
 		if (cN >= cT && cN >= cS) {
 			if (phase == PH_NODE) {

@@ -134,8 +134,8 @@ void drt_scene_destroy(drt_scene* scene);
 int drt_renderer_create(int device, drt_renderer** out);
 int drt_renderer_set_stream(drt_renderer* r, void* cuda_stream); /* launch on a caller-owned stream (NULL = own stream) */
 int drt_renderer_set_flags(drt_renderer* r, uint32_t flags);
-/* Kernel selection for measurements: variant 2 = per-warp phase voting over NODE/TRI/SHADE steps (default; expanded
- * fp32 nodes when the scene has them), 3 = the same on the compressed nodes, 0 = flat per-thread state machine,
+/* Kernel selection for measurements: variant 4 = per-warp phase voting over NODE/TRI/SHADE steps, 6 blocks/SM (default;
+ * expanded fp32 nodes when the scene has them), 2 = the same without the register cap, 3 = compressed nodes, 0 = flat per-thread state machine,
  * 1 = per-sample bounce loop; block_threads = 0 (default 128) or a multiple of 32 up to 256. Results do not
  * depend on either. */
 int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads);

@@ -92,7 +92,7 @@ def test_primary_hits_bit_exact(drt, name):
     assert np.all(np.abs(sub[same] - g["tuv_stride4"][0][same]) <= 1e-4 * g["tuv_stride4"][0][same])
 
 
-@pytest.mark.parametrize("variant", [2, 3, 0, 1])
+@pytest.mark.parametrize("variant", [4, 2, 3, 0, 1])
 @pytest.mark.parametrize("name", SCENES)
 def test_accumulated_image_bit_exact(drt, name, variant):
     g = np.load(os.path.join(GOLDEN, "scene_%s.npz" % name))
