@@ -90,6 +90,23 @@ class ClockSampler:
                 "power_w_max": max(power), "samples": len(sm)}
 
 
+class stdout_to_stderr:
+    """The reference's loader prints to stdout (Scene.cu:43-54); the bench's stdout carries exactly one JSON line."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def __exit__(self, *a):
+        try:
+            ctypes.CDLL(None).fflush(None)
+        except Exception:
+            pass
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -104,7 +121,8 @@ def oracle_scene():
     import oracles as O
     orc = O.best_oracle()
     if orc.kind == "reference":
-        return orc, orc.load(SCENE_PATH, bins=8, leaf=20, iterative=False)
+        with stdout_to_stderr():
+            return orc, orc.load(SCENE_PATH, bins=8, leaf=20, iterative=False)
     import dustraytracer_b200 as drt
     s = drt.Scene()
     s.loadGLTFmodel(SCENE_PATH)
@@ -135,7 +153,8 @@ def ref_cuda_baseline(frames=8):
         L = ctypes.CDLL(path)
         L.refcuda_load.restype = ctypes.c_void_p
         L.refcuda_render.restype = ctypes.c_double
-        h = L.refcuda_load(SCENE_PATH.encode(), 8, 20)  # editor values: 8 bins, 20-triangle leaves (EditorLayer.cpp:53-54)
+        with stdout_to_stderr():
+            h = L.refcuda_load(SCENE_PATH.encode(), 8, 20)  # editor values: 8 bins, 20-triangle leaves (EditorLayer.cpp:53-54)
         cam = O.default_camera_bytes()
         st = O.settings_bytes(sun=WORKLOAD["sun"], bounces=WORKLOAD["bounces"], max_samples=100000)
         P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
@@ -153,13 +172,13 @@ def run_reference(args, rank):
     if rank != 0:
         return 0
     orc, oh = oracle_scene()
-    cores = orc.max_threads()
+    cores = os.cpu_count() or orc.max_threads()  # explicit: torchrun exports OMP_NUM_THREADS=1
     for w in range(args.warmup):
-        cpu_reference_step(orc, oh, 1 + w * REF_STEP_FRAMES, frames=REF_STEP_FRAMES)
+        cpu_reference_step(orc, oh, 1 + w * REF_STEP_FRAMES, frames=REF_STEP_FRAMES, threads=cores)
     rays_total, sec_total = 0, 0.0
     t0 = time.perf_counter()
     for k in range(args.steps):
-        rays, sec = cpu_reference_step(orc, oh, 1 + (args.warmup + k) * REF_STEP_FRAMES, frames=REF_STEP_FRAMES)
+        rays, sec = cpu_reference_step(orc, oh, 1 + (args.warmup + k) * REF_STEP_FRAMES, frames=REF_STEP_FRAMES, threads=cores)
         rays_total += rays
         sec_total += sec
     wall = time.perf_counter() - t0
@@ -301,14 +320,19 @@ def run_ours(args, rank, world, local_rank):
                     "algorithmic_bytes_per_ray": bytes_per_ray, "node_visits_per_ray": V, "tri_tests_per_ray": T,
                     "note": "scene is cache resident (42 KB): the binding roofline is SM issue rate, see profiles/ and DESIGN.md"}
         # ---- CPU baseline: bounded sample on the host cores ----
-        orc, oh = oracle_scene()
-        crays, csec = cpu_reference_step(orc, oh, 1, frames=CPU_SAMPLE_FRAMES)
-        cpu = {"value": crays / csec / 1e6, "unit": "Mrays/s", "cores": orc.max_threads(), "kind": orc.kind,
-               "sample": "%d of the 256 samples per pixel (frame indices 1..%d) of the same 1920x1080 frame, %.1f s"
-                         % (CPU_SAMPLE_FRAMES, CPU_SAMPLE_FRAMES, csec)}
+        cpu = None
+        if world == 1:  # reported baselines are measured at N=1 only (torchrun also pins OMP_NUM_THREADS=1)
+            orc, oh = oracle_scene()
+            ncores = os.cpu_count() or orc.max_threads()
+            crays, csec = cpu_reference_step(orc, oh, 1, frames=CPU_SAMPLE_FRAMES, threads=ncores)
+            cpu = {"value": crays / csec / 1e6, "unit": "Mrays/s", "cores": ncores, "kind": orc.kind,
+                   "sample": "%d of the 256 samples per pixel (frame indices 1..%d) of the same 1920x1080 frame, %.1f s"
+                             % (CPU_SAMPLE_FRAMES, CPU_SAMPLE_FRAMES, csec)}
         value = total_rays / (max_ms * 1e-3) / 1e6
+        refcuda = None
         try:
-            refcuda = ref_cuda_baseline()
+            if world == 1:
+                refcuda = ref_cuda_baseline()
         except Exception as e:  # measurement aid only
             refcuda = {"error": str(e)}
         if refcuda and "error" not in refcuda:

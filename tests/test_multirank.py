@@ -1,0 +1,71 @@
+"""The N>1 path on CPU: two `gloo` ranks run the sample-range sharding bench.py uses on the GPUs
+(rank g renders frame indices g+1, g+1+world, ... into a private accumulation buffer; ONE reduce of the sums to
+rank 0; display = sum / total samples). The per-pixel work is the device code compiled for the host
+(tests/hostemu), so this checks the host-side sharding / reduce / resolve logic without a GPU."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import oracles as O
+
+GOLDEN = os.path.join(O.ROOT, "tests", "golden")
+W, H, FRAMES = 64, 36, 8
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _rank_main(rank, world, port, out_path):
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    g = np.load(os.path.join(GOLDEN, "scene_room.npz"))
+    emu = O.HostEmu()
+    h = emu.load(O.scene_path("room"))
+    per_rank = FRAMES // world
+    # the frame schedule drt_renderer_set_frame_schedule(rank + 1, world) gives this rank
+    acc, cnt = emu.render(h, g["camera"], g["settings"], W, H, rank + 1, world, per_rank, strict=True, rtl=True, steps=1)
+    t = torch.from_numpy(acc.copy())
+    rays = torch.tensor([float(cnt[0]), float(cnt[1])], dtype=torch.float64)
+    dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)          # the one collective of the path
+    dist.all_reduce(rays, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        display = t.numpy() / np.float32(per_rank * world)  # drt_renderer_resolve(total samples)
+        np.savez(out_path, acc=t.numpy(), display=display, rays=rays.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+    emu.free(h)
+
+
+@pytest.mark.parametrize("world", [2])
+def test_two_gloo_ranks_shard_the_frames_and_reduce(tmp_path, world):
+    import torch.multiprocessing as mp
+    out_path = str(tmp_path / "rank0.npz")
+    mp.start_processes(_rank_main, args=(world, _free_port(), out_path), nprocs=world, join=True, start_method="spawn")
+    got = np.load(out_path)
+    g = np.load(os.path.join(GOLDEN, "scene_room.npz"))
+    emu = O.HostEmu()
+    h = emu.load(O.scene_path("room"))
+    full, cnt = emu.render(h, g["camera"], g["settings"], W, H, 1, 1, FRAMES, strict=True, rtl=True, steps=1)
+    # same set of samples; only the fp32 summation order differs (shard by shard instead of frame by frame)
+    tol = FRAMES * np.finfo(np.float32).eps * np.abs(full).max()
+    assert np.abs(got["acc"] - full).max() <= tol
+    assert int(got["rays"][0]) == cnt[0] and int(got["rays"][1]) == cnt[1]
+    assert np.allclose(got["display"], full / np.float32(FRAMES), atol=tol)
+    # and each shard is exactly the frames it owns, rendered alone
+    for rank in range(world):
+        alone = np.zeros(W * H * 3, np.float32)
+        for f in range(rank + 1, FRAMES + 1, world):
+            emu.render(h, g["camera"], g["settings"], W, H, f, 1, 1, strict=True, rtl=True, steps=1, acc=alone)
+        shard, _ = emu.render(h, g["camera"], g["settings"], W, H, rank + 1, world, FRAMES // world, strict=True, rtl=True, steps=1)
+        assert np.array_equal(alone.view(np.uint32), shard.view(np.uint32))
+    emu.free(h)
