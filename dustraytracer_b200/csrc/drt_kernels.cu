@@ -13,6 +13,8 @@
 //   variant 3  phased, Q8      the same on the compressed nodes regardless of scene size
 //   variant 4..6 phased        variant 2 compiled for 6..8 resident 128-thread blocks per SM (80 / 72 / 64 registers);
 //                              4 is the default: issue-slot utilisation rises with occupancy up to 6 blocks (profiles/)
+//   variant 7, 8 phased, Q8    variant 3 compiled for 8 / 6 blocks per SM; 7 is what scenes without expanded nodes get
+//                              (soup-10M is latency-bound: +17 % from the extra resident warps)
 // Warps cover 8x4 pixel tiles (coherent primary rays); blocks are rows of such tiles.
 #include "drt_kernels.h"
 #include "drt_shade.cuh"
@@ -58,7 +60,7 @@ __device__ __forceinline__ void flush_counters(Counters* c, const PathCounters& 
 }
 
 template <bool STRICT, bool STATS, int VARIANT>
-__global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT >= 4 ? VARIANT + 2 : 1) k_render(const __grid_constant__ RenderParams P, const bool rtl, const int warps_per_block,
+__global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (VARIANT == 8 ? 6 : (VARIANT >= 4 ? VARIANT + 2 : 1))) k_render(const __grid_constant__ RenderParams P, const bool rtl, const int warps_per_block,
 	const PhasedTuning tune)
 {
 	int x, y;
@@ -74,7 +76,7 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT >= 4 ? VARIA
 		const size_t p = (size_t)x + (size_t)y * (size_t)P.width;
 		V3 acc = mk3(0.f, 0.f, 0.f);
 		if (valid) { const float4 a4 = P.accum[p]; acc = mk3(a4.x, a4.y, a4.z); }
-		acc = render_warp_phased<STRICT, STATS, VARIANT != 3 ? NODE_FMT_F32 : NODE_FMT_Q8>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st);
+		acc = render_warp_phased<STRICT, STATS, (VARIANT == 3 || VARIANT >= 7) ? NODE_FMT_Q8 : NODE_FMT_F32>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st);
 		if (valid) {
 			P.accum[p] = make_float4(acc.x, acc.y, acc.z, 0.f);
 			P.display[p] = make_float4(acc.x / P.total_samples, acc.y / P.total_samples, acc.z / P.total_samples, 1.f);
@@ -188,8 +190,12 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	// the phased kernels implement NORMALMODE; the debug views go through the reference-shaped loop
 	int variant = cfg.variant;
 	if (variant >= 2 && P.shade.render_mode != DRT_RENDER_NORMAL) variant = 1;
-	if ((variant == 2 || variant >= 4) && P.scene.nodes_f32 == nullptr) variant = 3;
-	if (variant >= 4 && threads != 128) variant = 2;
+	if ((variant == 2 || (variant >= 4 && variant <= 6)) && P.scene.nodes_f32 == nullptr) variant = threads == 128 ? 7 : 3;
+	if (variant >= 7 && threads != 128) variant = 3;
+	if (variant >= 4 && variant <= 6 && threads != 128) variant = 2;
+	if (variant == 7) k_render<STRICT, STATS, 7><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+	else if (variant == 8) k_render<STRICT, STATS, 8><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+	else
 	if (variant == 4) k_render<STRICT, STATS, 4><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else if (variant == 5) k_render<STRICT, STATS, 5><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else if (variant == 6) k_render<STRICT, STATS, 6><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);

@@ -157,7 +157,7 @@ def test_full_size_properties(drt):
     cam = drt.Camera()
     st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=8, max_samples=100000)
 
-    def run(first, stride, n, batch, flags=0, variant=0):
+    def run(first, stride, n, batch, flags=0, variant=4):
         r = drt.Renderer(flags=flags)
         r.set_tuning(variant, 0)
         r.m_RendererSettings = st
@@ -179,10 +179,24 @@ def test_full_size_properties(drt):
     s1, c1 = run(2, 2, 2, 2)
     assert c0["closest_rays"] + c1["closest_rays"] == ca["closest_rays"]
     assert np.abs((s0 + s1) - a).max() <= 4 * np.finfo(np.float32).eps * np.abs(a).max()
-    # strict arithmetic: both kernel variants agree bit for bit at full size
-    v0, _ = run(1, 1, 2, 2, flags=STRICT, variant=0)
-    v1, _ = run(1, 1, 2, 2, flags=STRICT, variant=1)
-    assert np.array_equal(bits(v0), bits(v1))
+    # strict arithmetic: every kernel variant agrees bit for bit at full size ...
+    v4, c4 = run(1, 1, 2, 2, flags=STRICT, variant=4)
+    for variant in (0, 1, 3):
+        v, c = run(1, 1, 2, 2, flags=STRICT, variant=variant)
+        assert np.array_equal(bits(v4), bits(v)) and c["closest_rays"] == c4["closest_rays"], variant
+    # ... and with the host-compiled reference (2 of the 256 frames of the 1080p image, a few seconds of CPU)
+    orc = O.best_oracle()
+    cam_f = O.default_camera_bytes()
+    st_b = O.settings_bytes(sun=True, bounces=8, max_samples=100000)
+    if orc.kind == "reference":
+        oh = orc.load(O.scene_path("room"))
+    else:
+        mats = np.frombuffer(b"".join(bytes(m) for m in scene.materials()), np.uint32).reshape(-1, 11).copy()
+        oh = orc.create(scene.triangles(), mats, [])
+    ref, rays, _ = orc.render(oh, cam_f, st_b, W, H, 1, 2)
+    orc.free(oh)
+    assert np.array_equal(bits(v4.reshape(-1)), bits(ref)), "full-size accumulation differs from the %s oracle" % orc.kind
+    assert c4["closest_rays"] == rays[0] and c4["shadow_rays"] == rays[1]
     assert np.isfinite(a).all() and a.min() >= 0
 
 
