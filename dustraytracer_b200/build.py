@@ -97,8 +97,21 @@ def build_oracle(force=False):
     return built
 
 
+CLI = os.path.join(PKG, "drt_render")
+
+
+def build_cli(force=False):
+    """g++ -> dustraytracer_b200/drt_render: command-line front end over include/drt.hpp (links libdrt.so by rpath)."""
+    src = os.path.join(ROOT, "tools", "drt_render.cpp")
+    deps = [src, os.path.join(ROOT, "include", "drt.hpp"), os.path.join(ROOT, "include", "drt.h"), LIB]
+    if not force and not _newer(CLI, deps):
+        return CLI
+    _run([_host_cxx(), "-std=c++17", "-O2", "-I", os.path.join(ROOT, "include"), src, "-o", CLI, "-L", PKG, "-ldrt", "-Wl,-rpath,$ORIGIN"])
+    return CLI
+
+
 def build_all(force=False, verbose=False):
-    out = [build_libdrt(force, verbose), build_hostemu(force)]
+    out = [build_libdrt(force, verbose), build_hostemu(force), build_cli(force)]
     out += build_oracle(force)
     return out
 

@@ -218,3 +218,18 @@ def test_from_triangles_host_side():
     t = s.triangles()
     assert t.shape == (2, 32) and s.stats()["materials"] == 1
     assert np.allclose(t[0, 28:31], (0, 0, 1)) and np.allclose(t[1, 28:31], (0, 0, -1))
+
+
+def test_cli_front_end_builds_and_fails_loudly_without_a_device(tmp_path):
+    """tools/drt_render.cpp over include/drt.hpp: compiles against the C ABI; with no GPU it must report the CUDA
+    error and exit non-zero (no CPU fallback)."""
+    import subprocess
+    from dustraytracer_b200 import build
+    exe = build.build_cli()
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "usage" in r.stderr
+    import torch
+    if not torch.cuda.is_available():
+        scene = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scenes", "room.glb")
+        r = subprocess.run([exe, scene, "--width", "32", "--height", "32", "--spp", "1"], capture_output=True, text=True)
+        assert r.returncode == 1 and "status -4" in r.stderr, r.stderr

@@ -284,3 +284,27 @@ def test_stats_counters(drt):
     rays = c["closest_rays"] + c["shadow_rays"]
     assert rays > 0 and c["node_visits"] >= rays and c["tri_tests"] > 0 and c["max_stack"] <= 48
     print("room: %.2f wide-node visits/ray, %.2f triangle tests/ray" % (c["node_visits"] / rays, c["tri_tests"] / rays))
+
+
+def test_cli_front_end_renders(drt, tmp_path):
+    """tools/drt_render.cpp (include/drt.hpp over the C ABI): renders to a PPM, reports rays; the 8-bit image equals
+    the API's DRT_RGBA8 readback of the same render."""
+    import json
+    import subprocess
+    from dustraytracer_b200 import build
+    exe = build.build_cli()
+    out = str(tmp_path / "room.ppm")
+    r = subprocess.run([exe, O.scene_path("room"), "--width", "160", "--height", "90", "--spp", "8", "--bounces", "8", "--sun", "--out", out],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    info = json.loads(r.stdout.strip().splitlines()[-1])
+    assert info["triangles"] == 330 and info["samples"] == 8 and info["rays"] > 160 * 90 * 8
+    raw = open(out, "rb").read()
+    assert raw.startswith(b"P6\n160 90\n255\n")
+    img = np.frombuffer(raw[len(b"P6\n160 90\n255\n"):], np.uint8).reshape(90, 160, 3)
+    rr = drt.Renderer()
+    rr.m_RendererSettings = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=8, max_samples=1 << 30)
+    rr.ResizeBuffer(160, 90)
+    rr.Render(drt.Camera(), gpu_scene(drt, "room"), 8)
+    api = rr.readback(drt.DRT_RGBA8)[::-1, :, :3]   # the PPM is written top-down
+    assert np.array_equal(img, api)
