@@ -113,8 +113,8 @@ struct LaneTrav {
 	uint32_t ng_base, ng_bits;   // current node group: child_base | (hit inner slots << 24 | imask)
 	uint32_t tri_base, tri_bits; // pending triangles of the last node
 	int sp;
-	Hit hit;
-	uint32_t best_id;
+	Hit hit; // only prim and t are carried between steps: u, v (and the id of the current winner, for exact-t ties)
+	         // are recomputed from the triangle where they are needed (same operations -> same bits)
 };
 
 #ifndef DRT_PSTACK
@@ -131,21 +131,23 @@ DRT_HD void trav_begin(LaneTrav& L, float tmax)
 	L.tri_base = 0u; L.tri_bits = 0u;
 	L.sp = 0;
 	L.hit.prim = -1; L.hit.t = tmax; L.hit.u = 0.f; L.hit.v = 0.f;
-	L.best_id = 0xffffffffu;
 }
 
 // Phase of a lane after a NODE or TRI step (pops the stack when the current group is exhausted).
 DRT_HD int trav_advance(LaneTrav& L, LaneStack& S)
 {
-	if (L.tri_bits != 0u) return PH_TRI;
-	if (L.ng_bits > 0x00ffffffu) return PH_NODE;
-	for (;;) {
-		if (L.sp == 0) return PH_SHADE;
-		--L.sp;
-		if (L.sp < DRT_PSTACK) break; // entries beyond the stack were dropped (counted via max_stack)
+	const bool has_tri = L.tri_bits != 0u, has_node = L.ng_bits > 0x00ffffffu;
+	int phase = has_tri ? PH_TRI : PH_NODE;
+	if (!has_tri && !has_node) {
+		if (L.sp == 0) phase = PH_SHADE;
+		else {
+			// entries beyond the stack were dropped when pushed (counted via max_stack): skip them in one step
+			const int sp = L.sp - 1;
+			L.sp = sp < DRT_PSTACK - 1 ? sp : DRT_PSTACK - 1;
+			L.ng_base = S.x[L.sp]; L.ng_bits = S.y[L.sp];
+		}
 	}
-	L.ng_base = S.x[L.sp]; L.ng_bits = S.y[L.sp];
-	return PH_NODE;
+	return phase;
 }
 
 // Picks the nearest pending inner child of the current group (octant order) and returns its node index.
@@ -309,19 +311,37 @@ DRT_HD bool tri_step(const SceneView& sc, const drt_f4* tris, LaneTrav& L, V3 o,
 	const uint32_t matw = as_uint(r1.w);
 	if (anyhit) {
 		if ((matw & 0x80000000u) && !alpha_accept<STRICT>(sc, slot, matw & 0x7fffffffu, u, v, st)) return false;
-		L.hit.prim = slot; L.hit.t = t; L.hit.u = u; L.hit.v = v;
+		L.hit.prim = slot; L.hit.t = t;
 		return true;
 	}
-	const uint32_t id = as_uint(r0.w);
 	if (!(t < L.hit.t)) {
 		if (!(t == L.hit.t) || L.hit.prim < 0) return false;
 		if (st) st->ties++;
-		if (!(id < L.best_id)) return false;
+		const uint32_t id = as_uint(r0.w), best_id = as_uint(ld_f4(tris + 3 * (size_t)L.hit.prim).w);
+		if (!(id < best_id)) return false;
 	}
 	if ((matw & 0x80000000u) && !alpha_accept<STRICT>(sc, slot, matw & 0x7fffffffu, u, v, st)) return false;
-	L.hit.prim = slot; L.hit.t = t; L.hit.u = u; L.hit.v = v;
-	L.best_id = id;
+	L.hit.prim = slot; L.hit.t = t;
 	return false;
+}
+
+// Barycentrics of the accepted hit, recomputed with the operations of tri_step (Intersection.cu:8-27) when a
+// textured material needs them: cheaper than carrying u, v through every step of every lane.
+template <bool STRICT>
+DRT_HD V2 hit_barycentrics(const drt_f4* tris, int slot, V3 o, V3 d)
+{
+	typedef M<STRICT> m;
+	const drt_f4* tp = tris + 3 * (size_t)slot;
+	const drt_f4 r0 = ld_f4(tp), r1 = ld_f4(tp + 1), r2 = ld_f4(tp + 2);
+	const V3 v0 = mk3(r0.x, r0.y, r0.z), e1 = mk3(r1.x, r1.y, r1.z), e2 = mk3(r2.x, r2.y, r2.z);
+	const V3 pvec = m::cross(d, e2);
+	const float det = m::dot(e1, pvec);
+	const float inv_det = m::div(1.0f, det);
+	const V3 tvec = m::sub3(o, v0);
+	const float u = m::mul(inv_det, m::dot(tvec, pvec));
+	const V3 qvec = m::cross(tvec, e1);
+	const float v = m::mul(inv_det, m::dot(d, qvec));
+	return mk2(u, v);
 }
 
 // Path state of one lane between steps (everything RayGen keeps in locals across its bounce loop).
@@ -379,7 +399,8 @@ DRT_HD bool shade_step(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, 
 			const int tex = (int)as_uint(mrec.w);
 			if (tex < 0) S.throughput = m::mul3(S.throughput, mk3(mrec.x, mrec.y, mrec.z));
 			else {
-				const V2 tuv = interp_uv<STRICT>(sc, hit.prim, hit.u, hit.v);
+				const V2 bc = hit_barycentrics<STRICT>(sc.tris, hit.prim, S.o, S.d);
+			const V2 tuv = interp_uv<STRICT>(sc, hit.prim, bc.x, bc.y);
 				S.throughput = m::mul3(S.throughput, texture_get_pixel<STRICT>(sc, tex, tuv, st));
 			}
 			const drt_f4 s0 = ld_f4(sc.shade + 3 * (size_t)hit.prim);
@@ -474,27 +495,23 @@ __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const Ph
 		ray_box_setup(S.o, S.d, R);
 		phase = first_phase;
 	}
-	for (;;) {
-		// two ballots over the bits of `phase` (NODE 0, TRI 1, SHADE 2, DONE 3) give the three lane sets
-		const unsigned b0 = __ballot_sync(0xffffffffu, (phase & 1) != 0), b1 = __ballot_sync(0xffffffffu, (phase & 2) != 0);
-		if ((b0 & b1) == 0xffffffffu) break;
-		const unsigned mN = ~(b0 | b1), mT = b0 & ~b1, mS = b1 & ~b0;
-		const int cN = mN ? __popc(mN) + T.bias_node : 0, cT = mT ? __popc(mT) + T.bias_tri : 0, cS = mS ? __popc(mS) + T.bias_shade : 0;
-		if (cN >= cT && cN >= cS) {
-			if (phase == PH_NODE) {
+	// two ballots over the bits of `phase` (NODE 0, TRI 1, SHADE 2, DONE 3) give the three lane sets; an empty set
+	// can only win the arg-max when all three are empty, which is the exit condition
+	unsigned b0 = __ballot_sync(0xffffffffu, (phase & 1) != 0), b1 = __ballot_sync(0xffffffffu, (phase & 2) != 0);
+	while ((b0 & b1) != 0xffffffffu) {
+		const int cN = __popc(~(b0 | b1)), cT = __popc(b0 & ~b1), cS = __popc(b1 & ~b0);
+		const int pick = (cN >= cT && cN >= cS) ? PH_NODE : (cT >= cS ? PH_TRI : PH_SHADE);
+		if (phase == pick) {
+			if (pick == PH_NODE) {
 				if (FMT == NODE_FMT_F32) node_step_f32<STATS>(P.scene.nodes_f32, L, K, R, st);
 				else node_step_q8<STATS>(P.scene.nodes, L, K, R, st);
 				phase = trav_advance(L, K);
 			}
-		}
-		else if (cT >= cS) {
-			if (phase == PH_TRI) {
+			else if (pick == PH_TRI) {
 				if (tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)) phase = PH_SHADE;
 				else phase = trav_advance(L, K);
 			}
-		}
-		else {
-			if (phase == PH_SHADE) {
+			else {
 				if (!shade_step<STRICT, STATS>(P, x, y, rtl, L.hit, S, pc, st)) phase = PH_DONE;
 				else {
 					ray_box_setup(S.o, S.d, R);
@@ -503,7 +520,10 @@ __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const Ph
 				}
 			}
 		}
+		b0 = __ballot_sync(0xffffffffu, (phase & 1) != 0);
+		b1 = __ballot_sync(0xffffffffu, (phase & 2) != 0);
 	}
+	(void)T;
 	return S.acc;
 }
 #endif
@@ -594,7 +614,8 @@ DRT_HD int hit_step(const RenderParams& P, const Hit& hit, LanePath5& S, PathCou
 	const int tex = (int)as_uint(mrec.w);
 	if (tex < 0) S.throughput = m::mul3(S.throughput, mk3(mrec.x, mrec.y, mrec.z));
 	else {
-		const V2 tuv = interp_uv<STRICT>(sc, hit.prim, hit.u, hit.v);
+		const V2 bc = hit_barycentrics<STRICT>(sc.tris, hit.prim, S.o, S.d);
+			const V2 tuv = interp_uv<STRICT>(sc, hit.prim, bc.x, bc.y);
 		S.throughput = m::mul3(S.throughput, texture_get_pixel<STRICT>(sc, tex, tuv, st));
 	}
 	const drt_f4 s0 = ld_f4(sc.shade + 3 * (size_t)hit.prim);
