@@ -186,7 +186,7 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	const long long tiles = (long long)((P.width + 7) / 8) * ((P.height + 3) / 4);
 	const unsigned blocks = (unsigned)((tiles + wpb - 1) / wpb);
 	PhasedTuning tune;
-	tune.bias_node = cfg.sched_bias[0]; tune.bias_tri = cfg.sched_bias[1]; tune.bias_shade = cfg.sched_bias[2];
+	tune.stick = cfg.sched_bias[0] > 0 ? cfg.sched_bias[0] : 6; // measured: room best at 8, dense_monkey at 4 (33 = never)
 	// the phased kernels implement NORMALMODE; the debug views go through the reference-shaped loop
 	int variant = cfg.variant;
 	if (variant >= 2 && P.shade.render_mode != DRT_RENDER_NORMAL) variant = 1;

@@ -11,7 +11,7 @@ struct LaunchConfig {
 	bool rtl = false;     // DRT_FLAG_HOST_ARG_ORDER
 	bool stats = false;   // DRT_FLAG_STATS
 	int variant = 4;      // render kernel variant (see drt_kernels.cu); 4 = default
-	int sched_bias[3] = { 0, 0, 0 }; // phased kernels: vote bias of NODE / TRI / SHADE
+	int sched_bias[3] = { 0, 0, 0 }; // phased kernels: [0] = sticky re-issue threshold (0 = default 6, 33 = never)
 	int block_threads = 0; // 0 = variant default
 };
 
