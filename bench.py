@@ -315,8 +315,10 @@ def run_ours(args, rank, world, local_rank):
         per_launch_ms = max_ms / args.steps
         rays_per_launch = total_rays / args.steps / world
         achieved = (bytes_per_ray * rays_per_launch + fb_bytes) / (per_launch_ms * 1e-3) / 1e9
+        ncu = ncu_capture_summary()
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                    "traffic": None, "peak_kind": peak_kind, "kernel": "k_render<flat>",
+                    "traffic": ncu.get("traffic"), "traffic_note": ncu.get("traffic_note"), "issue": ncu.get("issue"),
+                    "peak_kind": peak_kind, "kernel": "k_render<STRICT=0,STATS=0,VARIANT=%d> (phased, one launch per step)" % int(os.environ.get("DRT_VARIANT", "4")),
                     "algorithmic_bytes_per_ray": bytes_per_ray, "node_visits_per_ray": V, "tri_tests_per_ray": T,
                     "note": "scene is cache resident (42 KB): the binding roofline is SM issue rate, see profiles/ and DESIGN.md"}
         # ---- CPU baseline: bounded sample on the host cores ----
@@ -358,6 +360,34 @@ def run_ours(args, rank, world, local_rank):
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def ncu_capture_summary():
+    """DRAM bytes per launch and issue statistics of the render kernel from the committed `ncu --set full` capture
+    (profiles/r01c_render_phased_raw.txt; the capture itself is never part of a timed run)."""
+    path = os.path.join(ROOT, "profiles", "r01c_render_phased_raw.txt")
+    if not os.path.exists(path):
+        return {}
+    vals = {}
+    for line in open(path):
+        if " = " in line and not line.startswith("#"):
+            k, v = line.rsplit(" = ", 1)
+            name, _, unit = k.partition(" [")
+            try:
+                vals[name] = (float(v), unit.rstrip("]"))
+            except ValueError:
+                pass
+    scale = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
+    out = {}
+    if "dram__bytes_read.sum" in vals and "dram__bytes_write.sum" in vals:
+        out["traffic"] = sum(vals[k][0] * scale.get(vals[k][1], 1.0) for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+        out["traffic_note"] = ("bytes per launch, dram read+write of one k_render launch under ncu --set full (16-spp launch; "
+                               "a launch touches each frame-buffer pixel once whatever its sample count)")
+    if "smsp__issue_active.avg.pct_of_peak_sustained_active" in vals:
+        out["issue"] = {"issue_slot_fraction": vals["smsp__issue_active.avg.pct_of_peak_sustained_active"][0] / 100.0,
+                        "active_lanes_per_instruction": vals.get("smsp__thread_inst_executed_per_inst_executed.ratio", (None,))[0],
+                        "source": "profiles/r01c_render_phased_raw.txt"}
+    return out
 
 
 def main():

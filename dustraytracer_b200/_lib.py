@@ -68,6 +68,7 @@ _P = ctypes.POINTER
 # name -> (restype, argtypes); every symbol include/drt.h declares
 SIGNATURES = {
     "drt_scene_load_gltf": (_i, [ctypes.c_char_p, _P(_vp)]),
+    "drt_scene_load_gltf_ex": (_i, [ctypes.c_char_p, ctypes.c_uint32, _P(_vp)]),
     "drt_scene_from_triangles": (_i, [_vp, _vp, _vp, _sz, _vp, _sz, _P(_vp)]),
     "drt_scene_add_texture": (_i, [_vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _vp]),
     "drt_scene_build_bvh": (_i, [_vp, _P(drt_bvh_params), _i]),

@@ -79,11 +79,12 @@ class Scene:
     def __init__(self):
         self._h = ctypes.c_void_p()
 
-    def loadGLTFmodel(self, filepath):
+    def loadGLTFmodel(self, filepath, robust=False):
         """Scene::loadGLTFmodel (Scene.cu:181-317). Returns True; raises DrtError on failure
-        (the reference returns a bool its caller ignores)."""
+        (the reference returns a bool its caller ignores). robust=True reads the file as the glTF 2.0
+        specification says instead of as the reference loader does (drt_scene_load_gltf_ex, DRT_LOAD_ROBUST)."""
         self._free()
-        check(_lib.lib().drt_scene_load_gltf(str(filepath).encode(), ctypes.byref(self._h)))
+        check(_lib.lib().drt_scene_load_gltf_ex(str(filepath).encode(), 1 if robust else 0, ctypes.byref(self._h)))
         return True
 
     @classmethod

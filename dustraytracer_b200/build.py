@@ -26,7 +26,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC,-fno-fast-math,-ffp-contract=off",
 ]
 CUDA_SOURCES = ["drt_kernels.cu", "drt_api.cu"]
-HOST_SOURCES = ["drt_gltf.cpp", "drt_png.cpp"]
+HOST_SOURCES = ["drt_gltf.cpp", "drt_gltf_robust.cpp", "drt_png.cpp"]
 
 
 def _host_cxx():
@@ -77,7 +77,7 @@ def build_hostemu(force=False):
         return HOSTEMU
     os.makedirs(os.path.dirname(HOSTEMU), exist_ok=True)
     _run([_host_cxx(), "-std=c++17", "-O2", "-fPIC", "-fopenmp", "-ffp-contract=off", "-x", "c++", "-shared", "-Wl,-Bsymbolic", "-o", HOSTEMU,
-          src, os.path.join(CSRC, "drt_gltf.cpp"), os.path.join(CSRC, "drt_png.cpp"), "-lz"])
+          src] + [os.path.join(CSRC, f) for f in HOST_SOURCES] + ["-lz"])
     return HOSTEMU
 
 

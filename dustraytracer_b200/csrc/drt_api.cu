@@ -137,14 +137,17 @@ const char* drt_version(void) { return "dustraytracer_b200 0.1 (sm_100a)"; }
 void drt_default_camera(drt_camera* out) { if (out) default_camera(out); }
 void drt_default_settings(drt_settings* out) { if (out) default_settings(out); }
 
-int drt_scene_load_gltf(const char* path, drt_scene** out)
+int drt_scene_load_gltf(const char* path, drt_scene** out) { return drt_scene_load_gltf_ex(path, DRT_LOAD_REFERENCE_COMPAT, out); }
+
+int drt_scene_load_gltf_ex(const char* path, uint32_t load_flags, drt_scene** out)
 {
 	if (!path || !out) return fail(DRT_ERR_INVALID, "drt_scene_load_gltf: null argument");
+	if (load_flags & ~(uint32_t)DRT_LOAD_ROBUST) return fail(DRT_ERR_INVALID, "drt_scene_load_gltf_ex: unknown load flag");
 	*out = nullptr;
 	auto t0 = std::chrono::steady_clock::now();
 	drt_scene* s = new drt_scene();
 	std::string err;
-	int rc = load_gltf(path, s->host, err);
+	int rc = load_gltf(path, s->host, err, load_flags);
 	if (rc != DRT_OK) { delete s; return fail(rc, err); }
 	fill_stats(s);
 	s->stats.load_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();

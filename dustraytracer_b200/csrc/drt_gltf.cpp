@@ -87,12 +87,18 @@ bool load_uri(const std::string& base_dir, const std::string& uri, std::vector<u
 	return read_file(base_dir + decoded, out);
 }
 
-struct View { int buffer; size_t offset, length; };
+struct View { int buffer; size_t offset, length, stride; };
 
 } // namespace
 
-int load_gltf(const char* path, HostScene& out, std::string& err)
+// drt_gltf_robust.cpp: spec-conforming geometry walk (scene graph, transforms, accessors); SURVEY.md 8(f) rank 1
+int emit_robust_geometry(const JsonValue& root, const std::vector<const uint8_t*>& bdata, const std::vector<size_t>& blen,
+	HostScene& out, std::string& err);
+int remap_robust_materials(const JsonValue& root, const std::vector<bool>& image_ok, HostScene& out, std::string& err);
+
+int load_gltf(const char* path, HostScene& out, std::string& err, unsigned flags)
 {
+	const bool robust = (flags & DRT_LOAD_ROBUST) != 0;
 	std::vector<uint8_t> file;
 	if (!read_file(path, file)) { err = std::string("cannot read ") + path; return DRT_ERR_IO; }
 	std::string spath(path);
@@ -149,6 +155,7 @@ int load_gltf(const char* path, HostScene& out, std::string& err)
 		views[i].buffer = v.get_int("buffer", 0);
 		views[i].offset = (size_t)v.get_num("byteOffset", 0);
 		views[i].length = (size_t)v.get_num("byteLength", 0);
+		views[i].stride = (size_t)v.get_num("byteStride", 0);
 		if (views[i].buffer < 0 || (size_t)views[i].buffer >= bdata.size() || views[i].offset + views[i].length > blen[views[i].buffer]) {
 			err = "bufferView out of range"; return DRT_ERR_FORMAT;
 		}
@@ -158,6 +165,7 @@ int load_gltf(const char* path, HostScene& out, std::string& err)
 
 	// ---- images -> textures (Scene.cu:88-117: one Texture per IMAGE, in image order) ----
 	const JsonValue& jimages = arr("images");
+	std::vector<bool> image_ok(jimages.size(), true);
 	for (size_t i = 0; i < jimages.size(); i++) {
 		const JsonValue& img = jimages.arr[i];
 		HostTexture tex;
@@ -171,6 +179,12 @@ int load_gltf(const char* path, HostScene& out, std::string& err)
 			else perr = "cannot load image " + img.get_str("uri");
 		}
 		else perr = "image without bufferView/uri";
+		if (!ok && robust) { // e.g. JPEG: keep the slot so image indices stay stable, detach the materials that use it
+			out.warnings.push_back("image " + std::to_string(i) + " not decoded (" + perr + "); materials using it fall back to their factor");
+			image_ok[i] = false;
+			tex = HostTexture();
+			ok = true;
+		}
 		if (!ok) { err = "image " + std::to_string(i) + ": " + perr; return DRT_ERR_FORMAT; }
 		out.textures.push_back(std::move(tex));
 	}
@@ -199,6 +213,12 @@ int load_gltf(const char* path, HostScene& out, std::string& err)
 		m.refractive_index = 1.45f; // Material.cuh:21
 		m.metallic = metallic > 0 ? 1 : 0;
 		out.materials.push_back(m);
+	}
+
+	if (robust) {
+		int rc = remap_robust_materials(root, image_ok, out, err);
+		if (rc != DRT_OK) return rc;
+		return emit_robust_geometry(root, bdata, blen, out, err);
 	}
 
 	// ---- nodes -> meshes -> primitives (Scene.cu:120-178,192-314) ----

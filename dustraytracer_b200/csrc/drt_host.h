@@ -30,7 +30,8 @@ struct HostScene {
 
 bool decode_png(const uint8_t* data, size_t len, HostTexture& out, std::string& err);
 // Loads .glb / .gltf with the reference loader's semantics (Scene.cu:22-317).
-int load_gltf(const char* path, HostScene& out, std::string& err);
+// flags = drt_load_flags: DRT_LOAD_ROBUST switches to the spec-conforming ingest (drt_gltf_robust.cpp).
+int load_gltf(const char* path, HostScene& out, std::string& err, unsigned flags = 0);
 // face_normal = normalize(+-cross(p1-p0, p2-p0)) oriented to the mean vertex normal (Scene.cu:275-300).
 void compute_face_normal(const float* p9, const float* n9, float* out3);
 

@@ -113,6 +113,16 @@ typedef enum drt_flags {
 
 /* ---- scene: replaces Scene::loadGLTFmodel (Scene.cu:181-317) and BVHBuilder::build* (BVHBuilder.cu:11-145) ---- */
 int drt_scene_load_gltf(const char* path, drt_scene** out);
+/* The step before the path. load_flags = 0 is drt_scene_load_gltf (the reference loader's exact
+ * behaviour, quirks included: Scene.cu:120-178,192-207). DRT_LOAD_ROBUST reads the file as the glTF 2.0 specification
+ * says: node hierarchy + transforms of the default scene, accessor byteOffset / bufferView byteStride / any buffer,
+ * u8/u16/u32 or no indices, strips and fans, missing NORMAL / TEXCOORD_0, normalised integer attributes,
+ * texture -> image indirection, alphaMode OPAQUE / MASK(alphaCutoff) / BLEND(= the reference's cut-out rule). */
+typedef enum drt_load_flags {
+	DRT_LOAD_REFERENCE_COMPAT = 0,
+	DRT_LOAD_ROBUST = 1
+} drt_load_flags;
+int drt_scene_load_gltf_ex(const char* path, uint32_t load_flags, drt_scene** out);
 /* Synthetic soups: pos 9 floats/tri, uv 6 floats/tri or NULL, material index per tri or NULL. */
 int drt_scene_from_triangles(const float* pos, const float* uv, const int32_t* material_index, size_t n_tris,
 	const drt_material* materials, size_t n_materials, drt_scene** out);

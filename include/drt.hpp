@@ -41,11 +41,11 @@ public:
 	Scene& operator=(const Scene&) = delete;
 	~Scene() { drt_scene_destroy(h_); }
 
-	bool loadGLTFmodel(const char* filepath)
+	bool loadGLTFmodel(const char* filepath, uint32_t load_flags = DRT_LOAD_REFERENCE_COMPAT)
 	{
 		drt_scene_destroy(h_);
 		h_ = nullptr;
-		return drt_scene_load_gltf(filepath, &h_) == DRT_OK; // the reference returns bool and its caller ignores it
+		return drt_scene_load_gltf_ex(filepath, load_flags, &h_) == DRT_OK; // the reference returns bool and its caller ignores it
 	}
 	void fromTriangles(const float* pos9, const float* uv6, const int32_t* material_index, size_t n, const drt_material* mats, size_t n_mats)
 	{

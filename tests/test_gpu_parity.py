@@ -308,3 +308,28 @@ def test_cli_front_end_renders(drt, tmp_path):
     rr.Render(drt.Camera(), gpu_scene(drt, "room"), 8)
     api = rr.readback(drt.DRT_RGBA8)[::-1, :, :3]   # the PPM is written top-down
     assert np.array_equal(img, api)
+    # --out x.png: same pixels through the built-in PNG writer (stored deflate), and --robust drops room.glb's 8 zero-area triangles
+    import struct
+    import zlib
+    outp = str(tmp_path / "room.png")
+    r = subprocess.run([exe, O.scene_path("room"), "--width", "160", "--height", "90", "--spp", "8", "--bounces", "8", "--sun", "--robust", "--out", outp],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert json.loads(r.stdout.strip().splitlines()[-1])["triangles"] == 322
+    raw = open(outp, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat = 8, b""
+    while pos < len(raw):
+        n, ty = struct.unpack(">I4s", raw[pos:pos + 8])
+        body = raw[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(ty + body)
+        if ty == b"IHDR":
+            assert struct.unpack(">IIBBBBB", body) == (160, 90, 8, 2, 0, 0, 0)
+        if ty == b"IDAT":
+            idat += body
+        pos += 12 + n
+    rows = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(90, 1 + 160 * 3)
+    assert np.all(rows[:, 0] == 0)
+    png = rows[:, 1:].reshape(90, 160, 3)
+    # zero-area triangles cannot be hit, so dropping them changes the tree but not the picture beyond sampling-order noise
+    assert np.abs(png.astype(np.int32) - img.astype(np.int32)).mean() < 2.0

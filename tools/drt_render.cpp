@@ -1,7 +1,8 @@
 // drt_render -- headless command-line front end over include/drt.hpp (the step after the path: replaces the editor's
 // "save png", DustRayTracer/src/Editor/EditorLayer.cpp:23-31,85-97, and its hard-coded scene path, :50).
 //   drt_render scene.glb [--width W] [--height H] [--spp N] [--bounces B] [--sun] [--batch K] [--device D]
-//              [--pos x y z] [--dir x y z] [--out image.ppm|image.pfm]
+//              [--pos x y z] [--dir x y z] [--robust] [--out image.ppm|image.pfm|image.png]
+// --robust loads the file as the glTF specification says (DRT_LOAD_ROBUST) instead of as the reference loader does.
 // Prints one JSON line with build time, render time, rays and Mrays/s. Rows are written top-down (the frame
 // buffer's row 0 is the BOTTOM row, RenderKernel.cu:22-25 + EditorLayer.cpp:294-295 flip).
 #include <cstdio>
@@ -12,10 +13,58 @@
 
 #include "drt.hpp"
 
+// Minimal PNG writer (8-bit RGB, zlib "stored" blocks: no compression library needed); replaces stbi_write_png (EditorLayer.cpp:93-95).
+static void png_chunk(FILE* f, const char* type, const std::vector<uint8_t>& data)
+{
+	static uint32_t table[256];
+	if (!table[1])
+		for (uint32_t n = 0; n < 256; n++) {
+			uint32_t c = n;
+			for (int k = 0; k < 8; k++) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+			table[n] = c;
+		}
+	auto be32 = [&](uint32_t v) { const uint8_t b[4] = { (uint8_t)(v >> 24), (uint8_t)(v >> 16), (uint8_t)(v >> 8), (uint8_t)v }; fwrite(b, 1, 4, f); };
+	uint32_t crc = 0xffffffffu;
+	for (int i = 0; i < 4; i++) crc = table[(crc ^ (uint8_t)type[i]) & 0xff] ^ (crc >> 8);
+	for (uint8_t d : data) crc = table[(crc ^ d) & 0xff] ^ (crc >> 8);
+	be32((uint32_t)data.size());
+	fwrite(type, 1, 4, f);
+	if (!data.empty()) fwrite(data.data(), 1, data.size(), f);
+	be32(crc ^ 0xffffffffu);
+}
+
+// rows: top-down RGB, 3 * w bytes each
+static void write_png(FILE* f, uint32_t w, uint32_t h, const std::vector<uint8_t>& rgb)
+{
+	const uint8_t sig[8] = { 0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a };
+	fwrite(sig, 1, 8, f);
+	std::vector<uint8_t> ihdr = { (uint8_t)(w >> 24), (uint8_t)(w >> 16), (uint8_t)(w >> 8), (uint8_t)w, (uint8_t)(h >> 24), (uint8_t)(h >> 16), (uint8_t)(h >> 8), (uint8_t)h, 8, 2, 0, 0, 0 };
+	png_chunk(f, "IHDR", ihdr);
+	std::vector<uint8_t> raw;
+	raw.reserve((size_t)h * (3 * w + 1));
+	for (uint32_t y = 0; y < h; y++) { raw.push_back(0); raw.insert(raw.end(), rgb.begin() + (size_t)y * 3 * w, rgb.begin() + (size_t)(y + 1) * 3 * w); }
+	std::vector<uint8_t> z = { 0x78, 0x01 };
+	uint32_t a = 1, b = 0;
+	for (size_t p = 0; p < raw.size() || p == 0;) {
+		const size_t n = raw.size() - p < 65535 ? raw.size() - p : 65535;
+		const bool last = p + n >= raw.size();
+		z.push_back(last ? 1 : 0);
+		z.push_back((uint8_t)n); z.push_back((uint8_t)(n >> 8)); z.push_back((uint8_t)~n); z.push_back((uint8_t)(~n >> 8));
+		for (size_t i = 0; i < n; i++) { a = (a + raw[p + i]) % 65521u; b = (b + a) % 65521u; }
+		z.insert(z.end(), raw.begin() + p, raw.begin() + p + n);
+		p += n;
+		if (last) break;
+	}
+	const uint32_t adler = (b << 16) | a;
+	z.push_back((uint8_t)(adler >> 24)); z.push_back((uint8_t)(adler >> 16)); z.push_back((uint8_t)(adler >> 8)); z.push_back((uint8_t)adler);
+	png_chunk(f, "IDAT", z);
+	png_chunk(f, "IEND", {});
+}
+
 static int usage()
 {
 	fprintf(stderr, "usage: drt_render scene.glb [--width W] [--height H] [--spp N] [--bounces B] [--sun] [--batch K] [--device D]\n"
-		"                  [--pos x y z] [--dir x y z] [--out image.ppm|image.pfm]\n");
+		"                  [--pos x y z] [--dir x y z] [--robust] [--out image.ppm|image.pfm|image.png]\n");
 	return 2;
 }
 
@@ -25,6 +74,7 @@ int main(int argc, char** argv)
 	std::string scene_path = argv[1], out;
 	uint32_t W = 1280, H = 720, spp = 64, batch = 64;
 	int device = 0;
+	uint32_t load_flags = DRT_LOAD_REFERENCE_COMPAT;
 	drt::Camera cam;
 	drt::RendererSettings settings;
 	settings.max_samples = 1 << 30;
@@ -38,6 +88,7 @@ int main(int argc, char** argv)
 		else if (a == "--bounces") { need(1); settings.ray_bounce_limit = atoi(argv[++i]); }
 		else if (a == "--device") { need(1); device = atoi(argv[++i]); }
 		else if (a == "--sun") settings.enable_sunlight = 1;
+		else if (a == "--robust") load_flags = DRT_LOAD_ROBUST;
 		else if (a == "--out") { need(1); out = argv[++i]; }
 		else if (a == "--pos") { need(3); for (int k = 0; k < 3; k++) cam.position[k] = (float)atof(argv[++i]); }
 		else if (a == "--dir") { need(3); for (int k = 0; k < 3; k++) cam.forward_dir[k] = (float)atof(argv[++i]); }
@@ -45,7 +96,7 @@ int main(int argc, char** argv)
 	}
 	try {
 		drt::Scene scene;
-		if (!scene.loadGLTFmodel(scene_path.c_str())) throw drt::Error(DRT_ERR_IO, drt_last_error());
+		if (!scene.loadGLTFmodel(scene_path.c_str(), load_flags)) throw drt::Error(DRT_ERR_IO, drt_last_error());
 		drt::BVHBuilder builder;
 		builder.device = device;
 		builder.buildIterative(scene);
@@ -73,10 +124,14 @@ int main(int argc, char** argv)
 				for (size_t p = 0; p < (size_t)W * H; p++) fwrite(&px[4 * p], sizeof(float), 3, f);
 			}
 			else {
-				std::vector<uint8_t> px = renderer.readbackRGBA8();
-				fprintf(f, "P6\n%u %u\n255\n", W, H);
+				std::vector<uint8_t> px = renderer.readbackRGBA8(), rgb((size_t)W * H * 3);
 				for (uint32_t y = 0; y < H; y++)
-					for (uint32_t x = 0; x < W; x++) fwrite(&px[4 * ((size_t)(H - 1 - y) * W + x)], 1, 3, f);
+					for (uint32_t x = 0; x < W; x++) memcpy(&rgb[3 * ((size_t)y * W + x)], &px[4 * ((size_t)(H - 1 - y) * W + x)], 3);
+				if (out.size() > 4 && out.substr(out.size() - 4) == ".png") write_png(f, W, H, rgb);
+				else {
+					fprintf(f, "P6\n%u %u\n255\n", W, H);
+					fwrite(rgb.data(), 1, rgb.size(), f);
+				}
 			}
 			fclose(f);
 		}
