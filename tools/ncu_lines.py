@@ -1,7 +1,11 @@
 #!/usr/bin/env python3
 """Per-source-line summary of an ncu report (SASS page joined with nvdisasm line info of the SAME build).
 
-    python tools/ncu_lines.py gpurun_out/render_full.ncu-rep [kernel-substring] [--top N] > profiles/rNN_lines.txt
+    python tools/ncu_lines.py gpurun_out/render_full.ncu-rep [kernel-substring] [--top N]
+        [--regions "drt_phased.cuh:500-506=vote,154-226=node,..."] > profiles/rNN_lines.txt
+
+--regions sums program-order regions: an instruction inlined from another file (math, rng, intrinsics) is counted in
+the region of the last instruction before it (in SASS order) that maps to a listed line range of the region file.
 
 ncu's own CUDA-source page needs the source tree at the path the box compiled from; the GPU box has a scratch
 path, so we join by instruction offset instead: `ncu --page source --csv` gives per-SASS-instruction counters in
@@ -63,6 +67,16 @@ def main():
     base = int(body[0][0], 16)
     sass = {o: (f, l, t) for o, f, l, t in sass_lines(ksub)}
     agg = collections.defaultdict(lambda: [0, 0, 0, 0])  # inst, thread inst, samples, sass count
+    regions, rfile = [], None
+    if "--regions" in sys.argv:
+        spec = sys.argv[sys.argv.index("--regions") + 1]
+        rfile, _, rest = spec.partition(":")
+        for item in rest.split(","):
+            rng, _, name = item.partition("=")
+            lo, _, hi = rng.partition("-")
+            regions.append((int(lo), int(hi or lo), name))
+    ragg = collections.defaultdict(lambda: [0, 0, 0, 0, 0])  # inst, thread inst, samples, sass count, max executions of one instruction
+    cur = "(before first region line)"
     tot_i = tot_t = tot_s = 0
     miss = 0
     for r in body:
@@ -73,6 +87,14 @@ def main():
         ie, te, sm = int(r[col["Instructions Executed"]]), int(r[col["Thread Instructions Executed"]]), int(r[col["# Samples"]])
         a = agg[(f, l)]
         a[0] += ie; a[1] += te; a[2] += sm; a[3] += 1
+        if regions:
+            if f == rfile:
+                for lo, hi, name in regions:
+                    if lo <= l <= hi:
+                        cur = name
+                        break
+            g = ragg[cur]
+            g[0] += ie; g[1] += te; g[2] += sm; g[3] += 1; g[4] = max(g[4], ie)
         tot_i += ie; tot_t += te; tot_s += sm
     print("kernel %s: %d SASS instructions, %d unmatched; warp-inst executed %d, thread-inst %d (avg %.2f active lanes), samples %d"
           % (ksub, len(body), miss, tot_i, tot_t, tot_t / max(tot_i, 1), tot_s))
@@ -83,6 +105,12 @@ def main():
     print("\nper file:   %-22s %8s %8s %8s" % ("file", "inst%", "lanes", "stall%"))
     for f, b in sorted(byfile.items(), key=lambda kv: -kv[1][0]):
         print("            %-22s %7.2f%% %8.2f %7.2f%%" % (f, 100.0 * b[0] / tot_i, b[1] / max(b[0], 1), 100.0 * b[2] / max(tot_s, 1)))
+    if regions:
+        print("\nprogram-order regions of %s (inlined callees follow the caller's region):" % rfile)
+        print("  %-28s %5s %8s %8s %8s %12s %10s" % ("region", "sass", "inst%", "lanes", "stall%", "max issues", "inst/issue"))
+        for name, g in sorted(ragg.items(), key=lambda kv: -kv[1][0]):
+            print("  %-28s %5d %7.2f%% %8.2f %7.2f%% %12d %10.1f" % (name, g[3], 100.0 * g[0] / tot_i, g[1] / max(g[0], 1),
+                                                                100.0 * g[2] / max(tot_s, 1), g[4], g[0] / max(g[4], 1)))
     print("\ntop lines by issued warp instructions:")
     print("  %-22s %5s %5s %8s %8s %8s" % ("file", "line", "sass", "inst%", "lanes", "stall%"))
     for (f, l), a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
