@@ -19,7 +19,19 @@
 #include "drt_params.h"
 #include "drt_phased.cuh"
 
-#define DRT_F32_NODE_LIMIT 65536 // expanded nodes are kept for scenes up to this many wide nodes (16 MB)
+// Expanded 256-byte nodes are kept for scenes up to this many wide nodes (4 GB of the 180 GB). Measured on the soups
+// (profiles/r01c_soup_nodes.jsonl): 1.8 M wide nodes (464 MB expanded) still run 7 % faster than the 80-byte nodes,
+// 174 k nodes 19 % faster: the render kernel is issue-bound there too (DRAM 62 GB/s), so fewer instructions per child
+// test win over cache footprint.
+#define DRT_F32_NODE_LIMIT (1 << 24)
+
+// DRT_F32_NODE_LIMIT in the environment overrides the compiled-in limit (measurement knob: 256-byte nodes trade
+// cache footprint for ~3x fewer instructions per child test).
+static long long f32_node_limit()
+{
+	const char* e = getenv("DRT_F32_NODE_LIMIT");
+	return e && *e ? atoll(e) : (long long)DRT_F32_NODE_LIMIT;
+}
 
 namespace drt {
 
@@ -373,7 +385,7 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* /*par
 		DRT_CUDA(cudaMemcpyAsync(scene->nodes.p, wide_tmp.p, (size_t)res.wide_nodes * sizeof(WideNode), cudaMemcpyDeviceToDevice, stream));
 		// cache-resident scenes also get the de-quantised 256-byte nodes (issue-bound regime, drt_phased.cuh)
 		scene->nodes_f32.release();
-		if (res.wide_nodes <= DRT_F32_NODE_LIMIT) {
+		if ((long long)res.wide_nodes <= f32_node_limit()) {
 			DRT_CUDA(scene->nodes_f32.alloc((size_t)res.wide_nodes * DRT_F32NODE_F4));
 			DRT_CUDA(launch_expand_nodes(scene->nodes.p, scene->nodes_f32.p, res.wide_nodes, stream));
 		}

@@ -486,6 +486,86 @@ void emu_warp_sim(void* h, const drt_camera* cam, const drt_settings* st, int W,
 	out[11] += ts.nodes;
 }
 
+// Design tool (tools/sched_sim3.py): emulates ONE WARP of the three-step kernel actually shipped (render_warp_phased:
+// NODE / TRI / SHADE, full vote + sticky re-issue) over an 8x4 tile, with the policy as parameters:
+//   pol[0..2] = weight of the NODE / TRI / SHADE lane count in the arg-max
+//   pol[3..5] = eager threshold: if > 0 and at least this many lanes want TRI (pol[4]) / SHADE (pol[5]) / NODE (pol[3]),
+//               that step wins outright (checked in the order TRI, SHADE, NODE)
+//   pol[6..8] = sticky threshold per step (re-issue while at least this many lanes want it again; 33 = never)
+// out[0..2] = issues per step, out[3..5] = lane-steps per step, out[6] = full votes, out[7] = sticky ballots,
+// out[8] = rays, out[9] = sum over SHADE issues of the largest per-lane rejection-loop draw count (proxy of its cost)
+void emu_warp_sim3(void* h, const drt_camera* cam, const drt_settings* st, int W, int H, int tile_x, int tile_y, unsigned first,
+	unsigned n, const float* pol, unsigned long long* out)
+{
+	EmuScene* s = (EmuScene*)h;
+	RenderParams P = make_params(s, cam, st, W, H);
+	P.frame_first = first; P.frame_stride = 1; P.n_samples = n;
+	struct Lane { LanePath S; LaneTrav L; LaneStack K; RayBox R; int phase; uint32_t x, y; };
+	std::vector<Lane> lanes(32);
+	PathCounters pc; pc.closest = pc.shadow = 0;
+	TraceStats ts; memset(&ts, 0, sizeof(ts));
+	const int first_phase = P.scene.num_nodes > 0 ? PH_NODE : PH_SHADE;
+	for (int l = 0; l < 32; l++) {
+		Lane& A = lanes[l];
+		A.x = tile_x * 8 + (l & 7); A.y = tile_y * 4 + (l >> 3);
+		A.S.acc = mk3(0, 0, 0); A.S.k = 0; A.S.fn = mk3(0, 0, 0);
+		A.phase = PH_DONE;
+		trav_begin(A.L, FLT_MAX);
+		if ((int)A.x < W && (int)A.y < H && n > 0) {
+			path_begin_sample<false>(P, A.x, A.y, false, A.S);
+			ray_box_setup(A.S.o, A.S.d, A.R);
+			A.phase = first_phase;
+		}
+	}
+	for (;;) {
+		int c[3] = { 0, 0, 0 };
+		for (int l = 0; l < 32; l++) if (lanes[l].phase < 3) c[lanes[l].phase]++;
+		if (c[0] + c[1] + c[2] == 0) break;
+		out[6]++;
+		int pick = -1;
+		if (pol[4] > 0 && c[PH_TRI] >= pol[4]) pick = PH_TRI;
+		else if (pol[5] > 0 && c[PH_SHADE] >= pol[5]) pick = PH_SHADE;
+		else if (pol[3] > 0 && c[PH_NODE] >= pol[3]) pick = PH_NODE;
+		else {
+			float best = -1.f;
+			for (int k = 0; k < 3; k++) if (c[k] > 0 && c[k] * pol[k] > best) { best = c[k] * pol[k]; pick = k; }
+		}
+		for (;;) {
+			out[pick]++;
+			unsigned long long worst = 0;
+			for (int l = 0; l < 32; l++) {
+				Lane& A = lanes[l];
+				if (A.phase != pick) continue;
+				out[3 + pick]++;
+				if (pick == PH_NODE) {
+					node_step_f32<true>(P.scene.nodes_f32, A.L, A.K, A.R, &ts);
+					A.phase = trav_advance(A.L, A.K);
+				}
+				else if (pick == PH_TRI) {
+					if (tri_step<false, true>(P.scene, P.scene.tris, A.L, A.S.o, A.S.d, A.S.shadow, &ts)) A.phase = PH_SHADE;
+					else A.phase = trav_advance(A.L, A.K);
+				}
+				else {
+					const uint32_t seed0 = A.S.seed;
+					const bool more = shade_step<false, true>(P, A.x, A.y, false, A.L.hit, A.S, pc, &ts);
+					// draws consumed by this step = length of the pcg chain from seed0 to the new seed (bounded search)
+					unsigned long long draws = 0; uint32_t q = seed0;
+					while (q != A.S.seed && draws < 4096) { q = pcg_hash(q); draws++; }
+					if (draws < 4096 && draws > worst) worst = draws;
+					if (!more) A.phase = PH_DONE;
+					else { ray_box_setup(A.S.o, A.S.d, A.R); trav_begin(A.L, FLT_MAX); A.phase = first_phase; }
+				}
+			}
+			if (pick == PH_SHADE) out[9] += worst;
+			int again = 0;
+			for (int l = 0; l < 32; l++) if (lanes[l].phase == pick) again++;
+			out[7]++;
+			if (again < pol[6 + pick] || again == 0) break;
+		}
+	}
+	out[8] += pc.closest + pc.shadow;
+}
+
 void emu_camera_params(const drt_camera* cam, int W, int H, float* out20)
 {
 	CameraParams c = make_camera_params(*cam, W, H);
