@@ -76,7 +76,8 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 		const size_t p = (size_t)x + (size_t)y * (size_t)P.width;
 		V3 acc = mk3(0.f, 0.f, 0.f);
 		if (valid) { const float4 a4 = P.accum[p]; acc = mk3(a4.x, a4.y, a4.z); }
-		acc = render_warp_phased<STRICT, STATS, (VARIANT == 3 || VARIANT >= 7) ? NODE_FMT_Q8 : NODE_FMT_F32>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st);
+		__shared__ alignas(16) uint8_t lut[DRT_PERMUTE_LUT_BYTES];
+		acc = render_warp_phased<STRICT, STATS, (VARIANT == 3 || VARIANT >= 7) ? NODE_FMT_Q8 : NODE_FMT_F32>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st, lut);
 		if (valid) {
 			P.accum[p] = make_float4(acc.x, acc.y, acc.z, 0.f);
 			P.display[p] = make_float4(acc.x / P.total_samples, acc.y / P.total_samples, acc.z / P.total_samples, 1.f);

@@ -135,7 +135,7 @@ def main():
         img = r.readback(drt.DRT_RGBA32F)
         out.update({"ms": round(ms, 3), "Mrays_s": round(rays / ms / 1e3, 1), "Msamples_s": round(W * H * spp / ms / 1e3, 1),
                     "rays": rays, "mean_ldr": round(float(img[:, :, :3].mean()), 5), "finite": bool(np.isfinite(img).all())})
-        ref_ms = ref_cuda(name, cam_bytes, O.settings_bytes(sun=bool(sun), bounces=bounces, max_samples=1 << 30), W, H, a.ref_frames)
+        ref_ms = ref_cuda(name, cam_bytes, O.settings_bytes(sun=bool(sun), bounces=bounces, max_samples=1 << 30), W, H, a.ref_frames) if a.ref_frames > 0 else None
         if ref_ms:
             out["ref_cuda_fast_ms_per_sample"] = round(ref_ms, 4)
             out["speedup_vs_ref_cuda_fast"] = round(ref_ms / (ms / spp), 2)
