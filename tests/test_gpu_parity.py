@@ -333,3 +333,34 @@ def test_cli_front_end_renders(drt, tmp_path):
     png = rows[:, 1:].reshape(90, 160, 3)
     # zero-area triangles cannot be hit, so dropping them changes the tree but not the picture beyond sampling-order noise
     assert np.abs(png.astype(np.int32) - img.astype(np.int32)).mean() < 2.0
+
+
+@pytest.mark.parametrize("name", ["cornell_box", "animemaid"])
+def test_debug_views_bit_exact(drt, name):
+    """RenderMode DEBUGMODE through the C ABI (RendererSettings.h:12-20; RayGen.cuh:137-161): albedo, normal,
+    barycentric and uv views are bit-exact against the host-compiled reference; the BVH heat view runs and is finite
+    (it counts the nodes of OUR tree, so it has no reference values)."""
+    orc = O.best_oracle()
+    if orc.kind != "reference":
+        pytest.skip("needs oracle/_ref/libdrt_ref.so")
+    W, H = 96, 64
+    cam_f = O.default_camera_bytes()
+    oh = orc.load(O.scene_path(name))
+    scene = gpu_scene(drt, name)
+    for mode in (0, 1, 2, 3):
+        st_b = O.settings_bytes(sun=True, bounces=3, render_mode=1, debug_mode=mode)
+        ref, _, _ = orc.render(oh, cam_f, st_b, W, H, 1, 2)
+        r = drt.Renderer(flags=STRICT)
+        r.m_RendererSettings = settings_from(drt, st_b)
+        r.ResizeBuffer(W, H)
+        r.Render(camera_from(drt, cam_f), scene, 2)
+        got = r.readback(drt.DRT_ACCUM_RGB32F).reshape(-1)
+        assert np.array_equal(bits(got), bits(ref)), "debug mode %d: max abs diff %g" % (mode, np.abs(got - ref).max())
+        assert r.counters()["shadow_rays"] == 0
+    r = drt.Renderer(flags=drt.DRT_FLAG_STATS)
+    r.m_RendererSettings = settings_from(drt, O.settings_bytes(render_mode=1, debug_mode=4))
+    r.ResizeBuffer(W, H)
+    r.Render(camera_from(drt, cam_f), scene)
+    heat = r.readback(drt.DRT_ACCUM_RGB32F)
+    assert np.isfinite(heat).all() and heat.max() > 0.05
+    orc.free(oh)

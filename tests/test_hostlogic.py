@@ -238,3 +238,26 @@ def test_builder_degenerate_inputs(emu):
     pid, _, _, _, _ = emu.trace_primary(h, O.default_camera_bytes(), 8, 8)
     assert (pid == -1).all()
     emu.free(h)
+
+
+@pytest.mark.parametrize("name", ["cornell_box", "animemaid"])
+def test_debug_views_match_the_reference(emu, name):
+    """RenderMode DEBUGMODE (RendererSettings.h:12-20; RayGen.cuh:137-161): the tree-independent views -- albedo,
+    normal, barycentric, uv -- are bit-exact against the host-compiled reference. (The two BVH heat views count
+    the visited nodes of whichever tree is traversed, so they cannot match a different tree.)"""
+    orc = O.best_oracle()
+    if orc.kind != "reference":
+        pytest.skip("needs oracle/_ref/libdrt_ref.so")
+    W, H = 96, 64
+    cam = O.default_camera_bytes()
+    oh = orc.load(O.scene_path(name))
+    h = emu.load(O.scene_path(name))
+    for mode in (0, 1, 2, 3):
+        st = O.settings_bytes(sun=True, bounces=3, render_mode=1, debug_mode=mode)
+        ref, _, _ = orc.render(oh, cam, st, W, H, 1, 2)
+        got, cnt = emu.render(h, cam, st, W, H, 1, 1, 2, strict=True, rtl=True)
+        assert np.array_equal(bits(got), bits(ref)), "debug mode %d" % mode
+        assert cnt[1] == 0, "no shadow rays in the debug views (RayGen.cuh:114)"
+        assert len(np.unique(got)) > 4
+    orc.free(oh)
+    emu.free(h)
