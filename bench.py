@@ -90,6 +90,29 @@ class ClockSampler:
                 "power_w_max": max(power), "samples": len(sm)}
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout. Native libraries loaded by this process print on their own (the
+    reference's loader and destructors: Scene.cu:43-54), and C stdio may flush late, so file descriptor 1 is pointed
+    at stderr for the whole run and the JSON line is written to a private duplicate of the original stdout."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_json_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 class stdout_to_stderr:
     """The reference's loader prints to stdout (Scene.cu:43-54); the bench's stdout carries exactly one JSON line."""
 
@@ -155,17 +178,23 @@ def ref_cuda_baseline(frames=8):
         L.refcuda_render.restype = ctypes.c_double
         with stdout_to_stderr():
             h = L.refcuda_load(SCENE_PATH.encode(), 8, 20)  # editor values: 8 bins, 20-triangle leaves (EditorLayer.cpp:53-54)
-        cam = O.default_camera_bytes()
-        st = O.settings_bytes(sun=WORKLOAD["sun"], bounces=WORKLOAD["bounces"], max_samples=100000)
-        P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
-        W, H = WORKLOAD["width"], WORKLOAD["height"]
-        L.refcuda_render(ctypes.c_void_p(h), P(cam), P(st), W, H, 1, 2, None)  # warm-up
-        acc = np.zeros(W * H * 3, np.float32)
-        ms = L.refcuda_render(ctypes.c_void_p(h), P(cam), P(st), W, H, 1, frames, P(acc))
-        out[key] = {"ms_per_sample": ms / frames, "samples_per_s": W * H * frames / (ms * 1e-3), "frames": frames,
-                    "mean_ldr": float(acc.mean() / frames)}
-        L.refcuda_free(ctypes.c_void_p(h))
+            out[key] = _ref_cuda_run(L, h, frames)
+            L.refcuda_free(ctypes.c_void_p(h))  # the reference's Scene destructor prints too
     return out or None
+
+
+def _ref_cuda_run(L, h, frames):
+    import numpy as np
+    import oracles as O
+    cam = O.default_camera_bytes()
+    st = O.settings_bytes(sun=WORKLOAD["sun"], bounces=WORKLOAD["bounces"], max_samples=100000)
+    P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    W, H = WORKLOAD["width"], WORKLOAD["height"]
+    L.refcuda_render(ctypes.c_void_p(h), P(cam), P(st), W, H, 1, 2, None)  # warm-up
+    acc = np.zeros(W * H * 3, np.float32)
+    ms = L.refcuda_render(ctypes.c_void_p(h), P(cam), P(st), W, H, 1, frames, P(acc))
+    return {"ms_per_sample": ms / frames, "samples_per_s": W * H * frames / (ms * 1e-3), "frames": frames,
+            "mean_ldr": float(acc.mean() / frames)}
 
 
 def run_reference(args, rank):
@@ -195,7 +224,7 @@ def run_reference(args, rank):
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": wall,
     }
-    print(json.dumps(line), flush=True)
+    emit_json_line(line)
     return 0
 
 
@@ -355,7 +384,7 @@ def run_ours(args, rank, world, local_rank):
             "reference_cuda_on_this_gpu": refcuda,
             "rays_per_step": total_rays / args.steps, "wall_s_timed_region": t_wall,
         }
-        print(json.dumps(line), flush=True)
+        emit_json_line(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -364,10 +393,12 @@ def run_ours(args, rank, world, local_rank):
 
 def ncu_capture_summary():
     """DRAM bytes per launch and issue statistics of the render kernel from the committed `ncu --set full` capture
-    (profiles/r01c_render_phased_raw.txt; the capture itself is never part of a timed run)."""
-    path = os.path.join(ROOT, "profiles", "r01c_render_phased_raw.txt")
-    if not os.path.exists(path):
+    (profiles/rNN*_render_phased_raw.txt, latest; the capture itself is never part of a timed run)."""
+    import glob
+    found = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_render_phased_raw.txt")))
+    if not found:
         return {}
+    path = found[-1]  # the latest capture of the default kernel
     vals = {}
     for line in open(path):
         if " = " in line and not line.startswith("#"):
@@ -386,7 +417,7 @@ def ncu_capture_summary():
     if "smsp__issue_active.avg.pct_of_peak_sustained_active" in vals:
         out["issue"] = {"issue_slot_fraction": vals["smsp__issue_active.avg.pct_of_peak_sustained_active"][0] / 100.0,
                         "active_lanes_per_instruction": vals.get("smsp__thread_inst_executed_per_inst_executed.ratio", (None,))[0],
-                        "source": "profiles/r01c_render_phased_raw.txt"}
+                        "source": os.path.relpath(path, ROOT)}
     return out
 
 
@@ -397,6 +428,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
+    claim_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
