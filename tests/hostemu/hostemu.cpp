@@ -500,7 +500,9 @@ void emu_warp_sim3(void* h, const drt_camera* cam, const drt_settings* st, int W
 	EmuScene* s = (EmuScene*)h;
 	RenderParams P = make_params(s, cam, st, W, H);
 	P.frame_first = first; P.frame_stride = 1; P.n_samples = n;
-	struct Lane { LanePath S; LaneTrav L; LaneStack K; RayBox R; int phase; uint32_t x, y; };
+	struct Lane { LanePath S; LaneTrav L; LaneStack K; RayBox R; int phase; uint32_t x, y; bool more; };
+	const bool split_end = pol[10] > 0; // four-step variant: NODE / TRI / SHADE / END (post-process + next camera ray)
+	bool ended_in_issue = false;
 	std::vector<Lane> lanes(32);
 	PathCounters pc; pc.closest = pc.shadow = 0;
 	TraceStats ts; memset(&ts, 0, sizeof(ts));
@@ -517,10 +519,64 @@ void emu_warp_sim3(void* h, const drt_camera* cam, const drt_settings* st, int W
 			A.phase = first_phase;
 		}
 	}
-	for (;;) {
+	auto run_step = [&](int pick) -> unsigned long long {
+		unsigned long long worst = 0;
+		for (int l = 0; l < 32; l++) {
+			Lane& A = lanes[l];
+			if (A.phase != pick) continue;
+			out[3 + pick]++;
+			if (pick == PH_NODE) {
+				node_step_f32<true>(P.scene.nodes_f32, A.L, A.K, A.R, &ts);
+				A.phase = trav_advance(A.L, A.K);
+			}
+			else if (pick == PH_TRI) {
+				if (tri_step<false, true>(P.scene, P.scene.tris, A.L, A.S.o, A.S.d, A.S.shadow, &ts)) A.phase = PH_SHADE;
+				else A.phase = trav_advance(A.L, A.K);
+			}
+			else {
+				const uint32_t seed0 = A.S.seed, k0 = A.S.k;
+				const bool more = shade_step<false, true>(P, A.x, A.y, false, A.L.hit, A.S, pc, &ts);
+				unsigned long long draws = 0; uint32_t q = seed0;
+				while (q != A.S.seed && draws < 4096) { q = pcg_hash(q); draws++; }
+				if (draws < 4096 && draws > worst) worst = draws;
+				const bool ended = !more || A.S.k != k0;
+				if (ended) ended_in_issue = true;
+				if (ended && split_end) { A.phase = 4; A.more = more; } // PH_END: the sample end becomes a step of its own
+				else if (!more) A.phase = PH_DONE;
+				else { ray_box_setup(A.S.o, A.S.d, A.R); trav_begin(A.L, FLT_MAX); A.phase = first_phase; }
+			}
+		}
+		return worst;
+	};
+	// pol[9] > 0: no vote at all -- every iteration runs NODE, then TRI, then SHADE for whichever lanes want them, a step
+	// being skipped while fewer than pol[3] / pol[4] / pol[5] lanes want it unless nothing else can run (out[6] = iterations)
+	while (pol[9] > 0) {
 		int c[3] = { 0, 0, 0 };
 		for (int l = 0; l < 32; l++) if (lanes[l].phase < 3) c[lanes[l].phase]++;
-		if (c[0] + c[1] + c[2] == 0) break;
+		if (c[0] + c[1] + c[2] == 0) { out[8] += pc.closest + pc.shadow; return; }
+		out[6]++;
+		bool ran = false;
+		for (int k = 0; k < 3; k++) {
+			int cnt = 0;
+			for (int l = 0; l < 32; l++) if (lanes[l].phase == k) cnt++;
+			if (cnt == 0 || cnt < pol[3 + k]) continue;
+			out[k]++;
+			const unsigned long long w = run_step(k);
+			if (k == PH_SHADE) out[9] += w;
+			ran = true;
+		}
+		if (!ran) { // everything below its threshold: run the fullest
+			int best = 0;
+			for (int k = 1; k < 3; k++) if (c[k] > c[best]) best = k;
+			out[best]++;
+			const unsigned long long w = run_step(best);
+			if (best == PH_SHADE) out[9] += w;
+		}
+	}
+	for (;;) {
+		int c[5] = { 0, 0, 0, 0, 0 };
+		for (int l = 0; l < 32; l++) if (lanes[l].phase != PH_DONE) c[lanes[l].phase]++;
+		if (c[0] + c[1] + c[2] + c[4] == 0) break;
 		out[6]++;
 		int pick = -1;
 		if (pol[4] > 0 && c[PH_TRI] >= pol[4]) pick = PH_TRI;
@@ -529,33 +585,24 @@ void emu_warp_sim3(void* h, const drt_camera* cam, const drt_settings* st, int W
 		else {
 			float best = -1.f;
 			for (int k = 0; k < 3; k++) if (c[k] > 0 && c[k] * pol[k] > best) { best = c[k] * pol[k]; pick = k; }
+			if (c[4] > 0 && c[4] * pol[11] > best) pick = 4;
+		}
+		if (pick == 4) { // END step: lanes move on to their next camera ray (the work itself was done inside shade_step)
+			out[11]++;
+			for (int l = 0; l < 32; l++) {
+				Lane& A = lanes[l];
+				if (A.phase != 4) continue;
+				out[12]++;
+				if (!A.more) A.phase = PH_DONE;
+				else { ray_box_setup(A.S.o, A.S.d, A.R); trav_begin(A.L, FLT_MAX); A.phase = first_phase; }
+			}
+			continue;
 		}
 		for (;;) {
 			out[pick]++;
-			unsigned long long worst = 0;
-			for (int l = 0; l < 32; l++) {
-				Lane& A = lanes[l];
-				if (A.phase != pick) continue;
-				out[3 + pick]++;
-				if (pick == PH_NODE) {
-					node_step_f32<true>(P.scene.nodes_f32, A.L, A.K, A.R, &ts);
-					A.phase = trav_advance(A.L, A.K);
-				}
-				else if (pick == PH_TRI) {
-					if (tri_step<false, true>(P.scene, P.scene.tris, A.L, A.S.o, A.S.d, A.S.shadow, &ts)) A.phase = PH_SHADE;
-					else A.phase = trav_advance(A.L, A.K);
-				}
-				else {
-					const uint32_t seed0 = A.S.seed;
-					const bool more = shade_step<false, true>(P, A.x, A.y, false, A.L.hit, A.S, pc, &ts);
-					// draws consumed by this step = length of the pcg chain from seed0 to the new seed (bounded search)
-					unsigned long long draws = 0; uint32_t q = seed0;
-					while (q != A.S.seed && draws < 4096) { q = pcg_hash(q); draws++; }
-					if (draws < 4096 && draws > worst) worst = draws;
-					if (!more) A.phase = PH_DONE;
-					else { ray_box_setup(A.S.o, A.S.d, A.R); trav_begin(A.L, FLT_MAX); A.phase = first_phase; }
-				}
-			}
+			ended_in_issue = false;
+			const unsigned long long worst = run_step(pick);
+			if (pick == PH_SHADE && ended_in_issue) out[10]++;
 			if (pick == PH_SHADE) out[9] += worst;
 			int again = 0;
 			for (int l = 0; l < 32; l++) if (lanes[l].phase == pick) again++;

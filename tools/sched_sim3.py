@@ -5,7 +5,7 @@ re-issue; render_warp_phased in drt_phased.cuh). CPU only.
 tests/hostemu emu_warp_sim3 runs one warp (an 8x4 pixel tile) with the REAL step functions under a vote policy and
 counts issues and lane-steps per step. This script sweeps policies and prints modelled warp instructions per ray:
     cost = NODE issues * cN + TRI issues * cT + SHADE issues * cS + (worst rejection-loop draws per SHADE issue) * cD
-           + full votes * cV + sticky ballots * cB
+           + full votes * cV + sticky ballots * cB + (SHADE issues in which a lane ends its sample + END issues) * cE
 
     python tools/sched_sim3.py [--scene room|dense_monkey|...|soup:100000] [--tiles 40] [--spp 8]
 """
@@ -44,6 +44,19 @@ POLICIES = [
     ("w T2 S0.5", (1, 2, 0.5), (0, 0, 0), (6, 4, 12)),
     ("w T4 S0.5", (1, 4, 0.5), (0, 0, 0), (6, 2, 12)),
     ("w N0.5 T1 S0.5", (0.5, 1, 0.5), (0, 0, 0), (12, 4, 12)),
+    # no vote: every iteration runs NODE, TRI, SHADE in turn for the lanes that want them (thresholds N T S)
+    ("cycle 1/1/1", (1, 1, 1), (1, 1, 1), (33, 33, 33), 1),
+    ("cycle 1/1/4", (1, 1, 1), (1, 1, 4), (33, 33, 33), 1),
+    ("cycle 1/1/8", (1, 1, 1), (1, 1, 8), (33, 33, 33), 1),
+    ("cycle 1/1/12", (1, 1, 1), (1, 1, 12), (33, 33, 33), 1),
+    ("cycle 4/4/8", (1, 1, 1), (4, 4, 8), (33, 33, 33), 1),
+    ("cycle 6/6/12", (1, 1, 1), (6, 6, 12), (33, 33, 33), 1),
+    ("cycle 8/4/12", (1, 1, 1), (8, 4, 12), (33, 33, 33), 1),
+    # four steps: the sample end (post-process, accumulate, next camera ray) leaves SHADE and is voted on its own (weight)
+    ("4-step END w1", (1, 1, 1), (0, 0, 0), (6, 6, 6), 0, 1.0),
+    ("4-step END w0.5", (1, 1, 1), (0, 0, 0), (6, 6, 6), 0, 0.5),
+    ("4-step END w0.25", (1, 1, 1), (0, 0, 0), (6, 6, 6), 0, 0.25),
+    ("4-step END w0.7", (1, 1, 1), (0, 0, 0), (6, 6, 6), 0, 0.7),
 ]
 
 
@@ -56,9 +69,9 @@ def main():
     ap.add_argument("--bounces", type=int, default=8)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
-    ap.add_argument("--cost", default="145,71,120,15,16,10", help="cN,cT,cS,cD,cV,cB")
+    ap.add_argument("--cost", default="132,71,70,15,16,10,190", help="cN,cT,cS,cD,cV,cB,cE")
     a = ap.parse_args()
-    cN, cT, cS, cD, cV, cB = [float(x) for x in a.cost.split(",")]
+    cN, cT, cS, cD, cV, cB, cE = [float(x) for x in a.cost.split(",")]
     emu = O.HostEmu()
     emu.L.emu_warp_sim3.restype = None
     cam = O.default_camera_bytes()
@@ -76,21 +89,30 @@ def main():
     W, H = a.width, a.height
     rng = np.random.default_rng(1)
     tiles = [(int(rng.integers(0, W // 8)), int(rng.integers(0, H // 4))) for _ in range(a.tiles)]
-    print("%-26s %9s %7s  %-22s %-17s %s" % ("policy", "winst/ray", "vs ship", "lanes/issue N T S", "issues/ray N T S", "votes+ballots/ray"))
+    print("%-40s %9s %7s  %-22s %-17s %s" % ("policy", "winst/ray", "vs ship", "lanes/issue N T S", "issues/ray N T S", "votes+ballots/ray"))
     base = None
-    for name, w, eager, stick in POLICIES:
-        out = (ctypes.c_ulonglong * 10)()
-        pol = np.array(list(w) + list(eager) + list(stick), np.float32)
+    for entry in POLICIES:
+        name, w, eager, stick = entry[:4]
+        cycle = entry[4] if len(entry) > 4 else 0
+        w_end = entry[5] if len(entry) > 5 else 0.0
+        out = (ctypes.c_ulonglong * 13)()
+        pol = np.array(list(w) + list(eager) + list(stick) + [cycle, 1.0 if w_end > 0 else 0.0, w_end], np.float32)
         for tx, ty in tiles:
             emu.L.emu_warp_sim3(h, P(cam), P(st), W, H, tx, ty, 1, a.spp, P(pol), out)
         ex = np.array(out[0:3], float)
         ln = np.array(out[3:6], float)
         votes, ballots, rays, worst = float(out[6]), float(out[7]), float(out[8]), float(out[9])
-        cost = ex[0] * cN + ex[1] * cT + ex[2] * cS + worst * cD + votes * cV + ballots * cB
+        ended_issues, end_issues, end_lanes = float(out[10]), float(out[11]), float(out[12])
+        if cycle:  # one loop iteration = three "does any lane want it" branches + one count, ~12 instructions
+            cost = ex[0] * cN + ex[1] * cT + ex[2] * cS + worst * cD + votes * 12.0
+        else:      # a SHADE issue in which some lane ends its sample also runs the sample end (cE) for those lanes
+            cost = ex[0] * cN + ex[1] * cT + ex[2] * cS + worst * cD + votes * cV + ballots * cB + (ended_issues + end_issues) * cE
+        if end_issues:
+            name += " (%.1f lanes/END)" % (end_lanes / end_issues)
         per_ray = cost / rays
         if base is None:
             base = per_ray
-        print("%-26s %9.1f %7.3f  %-22s %-17s %.3f" % (name, per_ray, per_ray / base, np.round(ln / np.maximum(ex, 1), 1),
+        print("%-40s %9.1f %7.3f  %-22s %-17s %.3f" % (name, per_ray, per_ray / base, np.round(ln / np.maximum(ex, 1), 1),
                                                     np.round(ex / rays, 3), (votes + ballots) / rays))
 
 
