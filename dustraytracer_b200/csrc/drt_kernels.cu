@@ -166,10 +166,140 @@ __global__ void k_expand_nodes(const WideNode* wide, drt_f4* out, int n)
 }
 
 // ---- builder passes: one thread per element, bodies in drt_build.cuh ----
+// The two per-primitive passes of a level (BIN, PARTITION) communicate through atomics on per-node words. Near the root
+// millions of primitives hit the same few words (soup-10M: 44 ms per pass per level). The index arrays keep the
+// primitives of a node contiguous, so a block's 256 primitives almost always belong to ONE node: the block aggregates
+// for that node in shared memory and touches the global words once per block; primitives of other nodes in the same
+// block take the plain per-primitive path of drt_build.cuh.
+#define DRT_BINS_PER_NODE (3 * DRT_BINS * DRT_BIN_WORDS)
+
+__device__ __forceinline__ void bin_prim_block(const BuildArrays& A, int i)
+{
+	__shared__ int sb[DRT_BINS_PER_NODE];
+	__shared__ int s_node;
+	for (int j = threadIdx.x; j < DRT_BINS_PER_NODE; j += blockDim.x) {
+		const int k = j % DRT_BIN_WORDS;
+		sb[j] = k == 0 ? 0 : (k <= 3 ? DRT_ENC_POS_INF : DRT_ENC_NEG_INF);
+	}
+	if (threadIdx.x == 0) {
+		const int i0 = blockIdx.x * blockDim.x;
+		int node = i0 < A.n ? A.pnode_in[i0] : -1;
+		if (node < A.level_start || node >= A.level_end || A.nodes[node].count <= DRT_SMALL_NODE) node = -1;
+		s_node = node;
+	}
+	__syncthreads();
+	const int bn = s_node;
+	if (i < A.n) {
+		const int node = A.pnode_in[i];
+		if (node != bn || bn < 0) bin_prim(A, i);
+		else {
+			const BuildNode& nd = A.nodes[node];
+			const int prim = A.idx_in[i];
+			const drt_f4 lo = A.tri_lo[prim], hi = A.tri_hi[prim];
+			const float c[3] = { 0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z) };
+			const int elo[3] = { enc_f(lo.x), enc_f(lo.y), enc_f(lo.z) }, ehi[3] = { enc_f(hi.x), enc_f(hi.y), enc_f(hi.z) };
+			for (int a = 0; a < 3; a++) {
+				const int bin = bin_of(c[a], dec_f(nd.clo[a]), dec_f(nd.chi[a]), DRT_BINS);
+				int* w = sb + (a * DRT_BINS + bin) * DRT_BIN_WORDS;
+				atomicAdd(w, 1);
+				atomicMin(w + 1, elo[0]); atomicMin(w + 2, elo[1]); atomicMin(w + 3, elo[2]);
+				atomicMax(w + 4, ehi[0]); atomicMax(w + 5, ehi[1]); atomicMax(w + 6, ehi[2]);
+			}
+		}
+	}
+	__syncthreads();
+	if (bn >= 0) {
+		int* nb = A.bins + (size_t)(A.splits[bn].bin_slot - A.bin_slot_base) * DRT_BINS_PER_NODE;
+		for (int j = threadIdx.x; j < DRT_BINS_PER_NODE; j += blockDim.x) {
+			const int k = j % DRT_BIN_WORDS;
+			if (sb[j - k] == 0) continue; // empty bin
+			if (k == 0) atomicAdd(nb + j, sb[j]);
+			else if (k <= 3) atomicMin(nb + j, sb[j]);
+			else atomicMax(nb + j, sb[j]);
+		}
+	}
+}
+
+__device__ __forceinline__ void partition_prim_block(const BuildArrays& A, int i)
+{
+	__shared__ int s_node, s_base[2];
+	__shared__ int s_warp[2][8];  // per-warp counts of left / right movers (blocks have 256 threads)
+	__shared__ int s_box[2][12];  // per child: centroid lo xyz, centroid hi xyz, box lo xyz, box hi xyz
+	if (threadIdx.x < 24) { const int k = threadIdx.x % 12; (&s_box[0][0])[threadIdx.x] = (k % 6) < 3 ? DRT_ENC_POS_INF : DRT_ENC_NEG_INF; }
+	if (threadIdx.x == 0) {
+		const int i0 = blockIdx.x * blockDim.x;
+		int node = i0 < A.n ? A.pnode_in[i0] : -1;
+		if (node < A.level_start || node >= A.level_end || A.nodes[node].left < 0 || A.nodes[node].count <= DRT_SMALL_NODE) node = -1;
+		s_node = node;
+	}
+	__syncthreads();
+	const int bn = s_node;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	bool mine = false, left = false;
+	int prim = 0;
+	float c[3] = { 0.f, 0.f, 0.f };
+	drt_f4 lo = { 0.f, 0.f, 0.f, 0.f }, hi = { 0.f, 0.f, 0.f, 0.f };
+	bool median = false;
+	if (i < A.n) {
+		const int node = A.pnode_in[i];
+		if (node != bn || bn < 0) partition_prim(A, i);
+		else {
+			mine = true;
+			const BuildNode& nd = A.nodes[node];
+			const BuildSplit sp = A.splits[node];
+			prim = A.idx_in[i];
+			lo = A.tri_lo[prim]; hi = A.tri_hi[prim];
+			c[0] = 0.5f * (lo.x + hi.x); c[1] = 0.5f * (lo.y + hi.y); c[2] = 0.5f * (lo.z + hi.z);
+			median = sp.axis < 0;
+			left = !median ? (bin_of(c[sp.axis], dec_f(nd.clo[sp.axis]), dec_f(nd.chi[sp.axis]), DRT_BINS) < sp.split_bin)
+				: (i - nd.start < sp.n_left);
+		}
+	}
+	const unsigned ml = __ballot_sync(0xffffffffu, mine && left), mr = __ballot_sync(0xffffffffu, mine && !left);
+	if (lane == 0) { s_warp[0][warp] = __popc(ml); s_warp[1][warp] = __popc(mr); }
+	if (mine) {
+		int* bx = s_box[left ? 0 : 1];
+		atomicMin(bx + 0, enc_f(c[0])); atomicMin(bx + 1, enc_f(c[1])); atomicMin(bx + 2, enc_f(c[2]));
+		atomicMax(bx + 3, enc_f(c[0])); atomicMax(bx + 4, enc_f(c[1])); atomicMax(bx + 5, enc_f(c[2]));
+		if (median) {
+			atomicMin(bx + 6, enc_f(lo.x)); atomicMin(bx + 7, enc_f(lo.y)); atomicMin(bx + 8, enc_f(lo.z));
+			atomicMax(bx + 9, enc_f(hi.x)); atomicMax(bx + 10, enc_f(hi.y)); atomicMax(bx + 11, enc_f(hi.z));
+		}
+	}
+	__syncthreads();
+	if (bn < 0) return;
+	BuildNode* kids = A.nodes + A.nodes[bn].left;
+	if (threadIdx.x < 2) { // one cursor bump per child per block
+		int total = 0;
+		for (int w = 0; w < 8; w++) total += s_warp[threadIdx.x][w];
+		s_base[threadIdx.x] = total ? atomicAdd(&kids[threadIdx.x].fill, total) : 0;
+	}
+	else if (threadIdx.x >= 32 && threadIdx.x < 56) { // child bounds, once per block
+		const int t = threadIdx.x - 32, side = t / 12, k = t % 12;
+		const int v = s_box[side][k];
+		BuildNode* cn = kids + side;
+		if (k < 3) { if (v != DRT_ENC_POS_INF) atomicMin(&cn->clo[k], v); }
+		else if (k < 6) { if (v != DRT_ENC_NEG_INF) atomicMax(&cn->chi[k - 3], v); }
+		else if (k < 9) { if (v != DRT_ENC_POS_INF) atomicMin(&cn->lo[k - 6], v); }
+		else { if (v != DRT_ENC_NEG_INF) atomicMax(&cn->hi[k - 9], v); }
+	}
+	__syncthreads();
+	if (mine) {
+		const int side = left ? 0 : 1;
+		int rank = __popc((left ? ml : mr) & ((1u << lane) - 1u));
+		for (int w = 0; w < warp; w++) rank += s_warp[side][w];
+		const int np = kids[side].start + s_base[side] + rank;
+		A.idx_out[np] = prim;
+		A.pnode_out[np] = A.nodes[bn].left + side;
+	}
+}
+
 template <int PASS>
 __global__ void __launch_bounds__(256) k_build(const BuildArrays A, const int* idx_final, int a, int b, int n)
 {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (PASS == PASS_BIN) { bin_prim_block(A, i); return; }             // (block-wide barriers inside: no early exit)
+	if (PASS == PASS_PARTITION) { partition_prim_block(A, i); return; }
 	if (i >= n) return;
 	if (PASS == PASS_PRIM_BOUNDS) prim_bounds(A, i);
 	else if (PASS == PASS_INIT_BINS) init_bin_word(A, i, a);
