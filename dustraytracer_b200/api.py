@@ -16,7 +16,7 @@ import ctypes
 import numpy as np
 
 from . import _lib
-from ._lib import (DRT_ACCUM_RGB32F, DRT_FLAG_HOST_ARG_ORDER, DRT_FLAG_STATS, DRT_FLAG_STRICT, DRT_RGBA8, DRT_RGBA32F,
+from ._lib import (DRT_ACCUM_RGB32F, DRT_FLAG_EXTENDED_MATERIALS, DRT_FLAG_HOST_ARG_ORDER, DRT_FLAG_STATS, DRT_FLAG_STRICT, DRT_RGBA8, DRT_RGBA32F,
                    DrtError, check, drt_bvh_params, drt_camera, drt_counters, drt_hit, drt_material, drt_scene_stats,
                    drt_settings)
 

@@ -107,7 +107,7 @@ struct drt_scene {
 	bool built = false;
 	DevBuf<WideNode> nodes;
 	DevBuf<drt_f4> nodes_f32;
-	DevBuf<drt_f4> tris, shade, materials;
+	DevBuf<drt_f4> tris, shade, materials, materials_ext;
 	DevBuf<TexDesc> texdesc;
 	DevBuf<uint32_t> texels;
 	SceneView view;
@@ -330,6 +330,10 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* /*par
 	if (!texdesc.empty()) DRT_CUDA(cudaMemcpyAsync(scene->texdesc.p, texdesc.data(), texdesc.size() * sizeof(TexDesc), cudaMemcpyHostToDevice, stream));
 	if (!texels.empty()) DRT_CUDA(cudaMemcpyAsync(scene->texels.p, texels.data(), texels.size() * 4, cudaMemcpyHostToDevice, stream));
 	DRT_CUDA(cudaMemcpyAsync(scene->materials.p, mats.data(), mats.size() * sizeof(drt_f4), cudaMemcpyHostToDevice, stream));
+	std::vector<float> mats_ext;
+	fill_materials_ext(h.materials, mats_ext);
+	DRT_CUDA(scene->materials_ext.alloc(mats_ext.size() / 4));
+	DRT_CUDA(cudaMemcpyAsync(scene->materials_ext.p, mats_ext.data(), mats_ext.size() * sizeof(float), cudaMemcpyHostToDevice, stream));
 
 	// ---- build inputs + scratch ----
 	DevBuf<float> d_pos, d_uv, d_fn;
@@ -398,7 +402,7 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* /*par
 
 	SceneView& v = scene->view;
 	v.nodes = (const drt_u4*)scene->nodes.p;
-	v.tris = scene->tris.p; v.shade = scene->shade.p; v.materials = scene->materials.p;
+	v.tris = scene->tris.p; v.shade = scene->shade.p; v.materials = scene->materials.p; v.materials_ext = scene->materials_ext.p;
 	v.textures = scene->texdesc.p; v.texels = scene->texels.p;
 	v.nodes_f32 = scene->nodes_f32.p;
 	v.num_tris = (int32_t)n; v.num_nodes = res.wide_nodes; v.num_materials = (int32_t)mats.size(); v.num_textures = (int32_t)texdesc.size();
@@ -559,6 +563,7 @@ static LaunchConfig launch_config(const drt_renderer* r)
 	cfg.strict = (r->flags & DRT_FLAG_STRICT) != 0;
 	cfg.rtl = (r->flags & DRT_FLAG_HOST_ARG_ORDER) != 0;
 	cfg.stats = (r->flags & DRT_FLAG_STATS) != 0;
+	cfg.ext_materials = (r->flags & DRT_FLAG_EXTENDED_MATERIALS) != 0;
 	cfg.variant = r->variant; cfg.block_threads = r->block_threads;
 	for (int i = 0; i < 3; i++) cfg.sched_bias[i] = r->sched_bias[i];
 	return cfg;

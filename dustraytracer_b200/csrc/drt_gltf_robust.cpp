@@ -335,6 +335,17 @@ int remap_robust_materials(const JsonValue& root, const std::vector<bool>& image
 	for (size_t i = 0; i < jmats->size() && i < out.materials.size(); i++) {
 		const JsonValue& jm = jmats->arr[i];
 		drt_material& m = out.materials[i];
+		// fields of the extended material model (DRT_FLAG_EXTENDED_MATERIALS): metallic as a threshold on the factor
+		// (the reference stores the factor in a bool, so any non-zero factor is "metallic" there), KHR extensions
+		if (const JsonValue* pbr = jm.get("pbrMetallicRoughness")) m.metallic = pbr->get_num("metallicFactor", 1.0) >= 0.5 ? 1 : 0;
+		if (const JsonValue* ext = jm.get("extensions")) {
+			if (const JsonValue* t = ext->get("KHR_materials_transmission")) m.transmission = t->get_num("transmissionFactor", 0.0) > 0.0 ? 1 : 0;
+			if (const JsonValue* t = ext->get("KHR_materials_ior")) m.refractive_index = (float)t->get_num("ior", 1.5);
+			if (const JsonValue* t = ext->get("KHR_materials_emissive_strength")) {
+				const float k = (float)t->get_num("emissiveStrength", 1.0);
+				for (int c = 0; c < 3; c++) m.emissive_factor[c] *= k;
+			}
+		}
 		int image = -1;
 		if (const JsonValue* pbr = jm.get("pbrMetallicRoughness"))
 			if (const JsonValue* t = pbr->get("baseColorTexture")) {

@@ -165,6 +165,32 @@ __global__ void k_expand_nodes(const WideNode* wide, drt_f4* out, int n)
 	expand_wide_node(wide[i], out + (size_t)DRT_F32NODE_F4 * i);
 }
 
+// DRT_FLAG_EXTENDED_MATERIALS: the reference-shaped sample loop with the extended shading branch (drt_shade.cuh).
+template <bool STRICT, bool STATS>
+__global__ void __launch_bounds__(256) k_render_ext(const __grid_constant__ RenderParams P, const bool rtl, const int warps_per_block)
+{
+	int x, y;
+	bool valid;
+	pixel_of_thread(P.width, P.height, warps_per_block, x, y, valid);
+	PathCounters pc;
+	pc.closest = 0; pc.shadow = 0;
+	TraceStats ts;
+	ts.nodes = ts.tris = ts.ties = ts.alpha = ts.max_stack = ts.clamps = 0;
+	TraceStats* st = STATS ? &ts : nullptr;
+	if (valid) {
+		const size_t p = (size_t)x + (size_t)y * (size_t)P.width;
+		const float4 a4 = P.accum[p];
+		V3 acc = mk3(a4.x, a4.y, a4.z);
+		for (uint32_t k = 0; k < P.n_samples; k++) {
+			const uint32_t frameidx = P.frame_first + k * P.frame_stride;
+			acc = M<STRICT>::add3(acc, path_radiance<STRICT, STATS, true>(P, (uint32_t)x, (uint32_t)y, frameidx, rtl, pc, st));
+		}
+		P.accum[p] = make_float4(acc.x, acc.y, acc.z, 0.f);
+		P.display[p] = make_float4(acc.x / P.total_samples, acc.y / P.total_samples, acc.z / P.total_samples, 1.f);
+	}
+	flush_counters(P.counters, pc, st);
+}
+
 // ---- builder passes: one thread per element, bodies in drt_build.cuh ----
 // The two per-primitive passes of a level (BIN, PARTITION) communicate through atomics on per-node words. Near the root
 // millions of primitives hit the same few words (soup-10M: 44 ms per pass per level). The index arrays keep the
@@ -320,6 +346,10 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	tune.stick = cfg.sched_bias[0] > 0 ? cfg.sched_bias[0] : 6; // measured: room best at 8, dense_monkey at 4 (33 = never)
 	// the phased kernels implement NORMALMODE; the debug views go through the reference-shaped loop
 	int variant = cfg.variant;
+	if (cfg.ext_materials && P.shade.render_mode == DRT_RENDER_NORMAL) {
+		k_render_ext<STRICT, STATS><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb);
+		return cudaGetLastError();
+	}
 	if (variant >= 2 && P.shade.render_mode != DRT_RENDER_NORMAL) variant = 1;
 	if ((variant == 2 || (variant >= 4 && variant <= 6)) && P.scene.nodes_f32 == nullptr) variant = threads == 128 ? 7 : 3;
 	if (variant >= 7 && threads != 128) variant = 3;

@@ -10,6 +10,7 @@ struct LaunchConfig {
 	bool strict = false;  // DRT_FLAG_STRICT
 	bool rtl = false;     // DRT_FLAG_HOST_ARG_ORDER
 	bool stats = false;   // DRT_FLAG_STATS
+	bool ext_materials = false; // DRT_FLAG_EXTENDED_MATERIALS: emissive / metal / dielectric shading (reference-shaped loop kernel)
 	int variant = 4;      // render kernel variant (see drt_kernels.cu); 4 = default
 	int sched_bias[3] = { 0, 0, 0 }; // phased kernels: [0] = sticky re-issue threshold (0 = default 6, 33 = never)
 	int block_threads = 0; // 0 = variant default

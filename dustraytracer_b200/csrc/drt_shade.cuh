@@ -57,8 +57,28 @@ DRT_HD V3 texture_get_pixel(const SceneView& sc, int tex, V2 uv, TraceStats* st)
 	return mk3(m::mul(r, r), m::mul(g, g), m::mul(b, b));
 }
 
+// Schlick reflectance and refraction: the reference's dead helpers (Random.cu:26-40), used by the extended materials.
+DRT_HD float schlick_reflectance(float cosine, float ri)
+{
+	float r0 = (1.f - ri) / (1.f + ri);
+	r0 = r0 * r0;
+	const float k = 1.f - cosine, k2 = k * k;
+	return r0 + (1.f - r0) * (k2 * k2 * k);
+}
+DRT_HD V3 refract_dir(V3 uv, V3 n, float etai_over_etat)
+{
+	typedef M<false> m;
+	const float cos_theta = fminf(-m::dot(uv, n), 1.0f);
+	const V3 perp = m::scale(m::add3(uv, m::scale(n, cos_theta)), etai_over_etat);
+	const V3 par = m::scale(n, -sqrtf(fabsf(1.0f - m::dot(perp, perp))));
+	return m::add3(perp, par);
+}
+
 // One call of the reference's RayGen: radiance of pixel (x, y) for frame index `frameidx`.
-template <bool STRICT, bool STATS>
+// EXT (DRT_FLAG_EXTENDED_MATERIALS, beyond the reference): emission is added at every hit, metals reflect about the
+// face normal with a roughness-scaled fuzz, dielectrics reflect or refract by Schlick's approximation; specular hits
+// take no sun sample. Diffuse, non-emissive materials shade exactly as without EXT (same random draws).
+template <bool STRICT, bool STATS, bool EXT = false>
 DRT_HD V3 path_radiance(const RenderParams& P, uint32_t x, uint32_t y, uint32_t frameidx, bool rtl,
 	PathCounters& pc, TraceStats* st)
 {
@@ -98,6 +118,7 @@ DRT_HD V3 path_radiance(const RenderParams& P, uint32_t x, uint32_t y, uint32_t 
 		const uint32_t mat = as_uint(r1.w) & 0x7fffffffu;
 		const drt_f4 mrec = ld_f4(sc.materials + mat);
 		const int tex = (int)as_uint(mrec.w);
+		const V3 throughput_in = throughput;
 		if (tex < 0) throughput = m::mul3(throughput, mk3(mrec.x, mrec.y, mrec.z));
 		else {
 			tex_uv = interp_uv<STRICT>(sc, hit.prim, hit.u, hit.v);
@@ -110,6 +131,31 @@ DRT_HD V3 path_radiance(const RenderParams& P, uint32_t x, uint32_t y, uint32_t 
 		const V3 pos = m::add3(ray.o, m::scale(ray.d, hit.t));
 		if (m::dot(fn, m::normalize(ray.d)) > 0.f) fn = m::scale(fn, -1.f);
 		const V3 new_o = m::add3(pos, m::scale(fn, 0.001f));
+
+		if (EXT && !debug) {
+			const drt_f4 e0 = ld_f4(sc.materials_ext + 2 * (size_t)mat), e1 = ld_f4(sc.materials_ext + 2 * (size_t)mat + 1);
+			light = m::add3(light, m::mul3(mk3(e0.x, e0.y, e0.z), throughput_in));
+			const uint32_t kind = as_uint(e0.w);
+			if (kind != 0u) {
+				const V3 dn = m::normalize(ray.d);
+				const V3 mirrored = m::sub3(dn, m::scale(fn, 2.f * m::dot(dn, fn)));
+				if (kind == 1u) { // metal: fuzzy mirror, absorbed when the fuzz pushes it below the surface
+					V3 dir = mirrored;
+					if (e1.x > 0.f) dir = m::add3(dir, m::scale(random_unit_sphere_vec3<STRICT>(seed, rtl), e1.x));
+					if (!(m::dot(dir, fn) > 0.f)) break;
+					ray.o = new_o; ray.d = dir;
+				}
+				else { // dielectric: fn faces the incoming ray; it was flipped when the ray leaves the medium
+					const bool entering = !(m::dot(mk3(s0.x, s0.y, s0.z), dn) > 0.f);
+					const float ri = entering ? 1.f / e1.y : e1.y;
+					const float cos_t = fminf(-m::dot(dn, fn), 1.f);
+					const float sin_t = sqrtf(fmaxf(0.f, 1.f - cos_t * cos_t));
+					if (ri * sin_t > 1.f || schlick_reflectance(cos_t, ri) > random_float(seed)) { ray.o = new_o; ray.d = mirrored; }
+					else { ray.o = m::sub3(pos, m::scale(fn, 0.001f)); ray.d = refract_dir(dn, fn, ri); }
+				}
+				continue;
+			}
+		}
 
 		if (S.enable_sunlight && S.render_mode == DRT_RENDER_NORMAL) {
 			V3 sd = m::add3(S.sunpos, m::scale(random_unit_vec3<STRICT>(seed, rtl), 1.5f));

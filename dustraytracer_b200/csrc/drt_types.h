@@ -49,6 +49,7 @@ struct SceneView {
 	const drt_f4* tris;
 	const drt_f4* shade;
 	const drt_f4* materials;
+	const drt_f4* materials_ext; // 2 / material: emissive.rgb | kind (0 diffuse, 1 metal, 2 dielectric); roughness, ior, 0, 0
 	const TexDesc* textures;
 	const uint32_t* texels;
 	int32_t num_tris, num_nodes, num_materials, num_textures;

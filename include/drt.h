@@ -108,7 +108,12 @@ typedef enum drt_format {
 typedef enum drt_flags {
 	DRT_FLAG_STRICT = 1,       /* separately-rounded fp32 in the reference's operation order (parity mode)      */
 	DRT_FLAG_HOST_ARG_ORDER = 2, /* draw randomUnitVec3 components right-to-left like the g++-compiled oracle     */
-	DRT_FLAG_STATS = 4         /* count node visits / triangle tests (slower; for the roofline's V and T terms) */
+	DRT_FLAG_STATS = 4,        /* count node visits / triangle tests (slower; for the roofline's V and T terms) */
+	DRT_FLAG_EXTENDED_MATERIALS = 8 /* opt-in, beyond the reference: shade the material fields the
+	                              reference loads but ignores (Material.cuh:10-22; RayGen.cuh never reads them):
+	                              emissive_factor, metallic + roughness (mirror / fuzzy reflection), transmission +
+	                              refractive_index (dielectric, with the reference's own dead helpers refract /
+	                              reflectance, Random.cu:26-40). Off: exactly the reference's shading. */
 } drt_flags;
 
 /* ---- scene: replaces Scene::loadGLTFmodel (Scene.cu:181-317) and BVHBuilder::build* (BVHBuilder.cu:11-145) ---- */

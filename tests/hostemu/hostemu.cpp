@@ -56,6 +56,7 @@ struct EmuScene {
 	HostScene host;
 	std::vector<int32_t> mat_flags;
 	std::vector<drt_f4> tri_lo, tri_hi, out_tris, out_shade, materials, nodes_f32;
+	std::vector<float> materials_ext;
 	std::vector<int> idx0, idx1, pn0, pn1, bins, wide_src;
 	std::vector<BuildNode> nodes;
 	std::vector<BuildSplit> splits;
@@ -96,6 +97,7 @@ void upload_tables(EmuScene* s)
 		else { m.x = m.y = m.z = 1.f; m.w = as_float((uint32_t)-1); } // default material for index -1
 		s->materials[i] = m;
 	}
+	fill_materials_ext(h.materials, s->materials_ext);
 	size_t n = h.tri_count();
 	s->mat_flags.resize(n);
 	for (size_t i = 0; i < n; i++) {
@@ -132,7 +134,7 @@ int build(EmuScene* s)
 	int rc = run_build(ex, A, s->result);
 	SceneView& v = s->view;
 	v.nodes = (const drt_u4*)s->wide.data();
-	v.tris = s->out_tris.data(); v.shade = s->out_shade.data(); v.materials = s->materials.data();
+	v.tris = s->out_tris.data(); v.shade = s->out_shade.data(); v.materials = s->materials.data(); v.materials_ext = (const drt_f4*)s->materials_ext.data();
 	v.textures = s->texdesc.data(); v.texels = s->texels.data();
 	s->nodes_f32.resize((size_t)DRT_F32NODE_F4 * (s->result.wide_nodes > 0 ? s->result.wide_nodes : 1));
 	for (int i = 0; i < s->result.wide_nodes; i++) expand_wide_node(s->wide[i], s->nodes_f32.data() + (size_t)DRT_F32NODE_F4 * i);
@@ -319,6 +321,33 @@ void emu_render_flat(void* h, const drt_camera* cam, const drt_settings* st, int
 			V3 in = mk3(a[0], a[1], a[2]);
 			V3 r = strict ? render_pixel_flat<true, false>(P, x, y, rtl != 0, in, pc, nullptr) : render_pixel_flat<false, false>(P, x, y, rtl != 0, in, pc, nullptr);
 			a[0] = r.x; a[1] = r.y; a[2] = r.z;
+		}
+		c0 += pc.closest; c1 += pc.shadow;
+	}
+	if (counters) { counters[0] = c0; counters[1] = c1; }
+}
+
+// The reference-shaped sample loop with the extended material branch (DRT_FLAG_EXTENDED_MATERIALS), production arithmetic.
+void emu_render_ext(void* h, const drt_camera* cam, const drt_settings* st, int W, int H, unsigned first, unsigned stride,
+	unsigned n, int strict, int rtl, float* acc, unsigned long long* counters)
+{
+	EmuScene* s = (EmuScene*)h;
+	RenderParams P = make_params(s, cam, st, W, H);
+	unsigned long long c0 = 0, c1 = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : c0, c1)
+	for (int y = 0; y < H; y++) {
+		PathCounters pc;
+		pc.closest = pc.shadow = 0;
+		TraceStats ts;
+		memset(&ts, 0, sizeof(ts));
+		for (int x = 0; x < W; x++) {
+			float* a = acc + 3 * ((size_t)x + (size_t)y * W);
+			for (unsigned k = 0; k < n; k++) {
+				const unsigned f = first + k * stride;
+				V3 c = strict ? path_radiance<true, true, true>(P, x, y, f, rtl != 0, pc, &ts) : path_radiance<false, true, true>(P, x, y, f, rtl != 0, pc, &ts);
+				if (strict) { a[0] = M<true>::add(a[0], c.x); a[1] = M<true>::add(a[1], c.y); a[2] = M<true>::add(a[2], c.z); }
+				else { a[0] += c.x; a[1] += c.y; a[2] += c.z; }
+			}
 		}
 		c0 += pc.closest; c1 += pc.shadow;
 	}

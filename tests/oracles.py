@@ -276,11 +276,16 @@ class HostEmu:
         self.L.emu_trace_primary(h, P(cam), W, H, frameidx, int(strict), int(rtl), P(hits), None, stats)
         return hits.view(np.int32)[:, 0].copy(), hits[:, 1].copy(), hits[:, 2].copy(), hits[:, 3].copy(), list(stats)
 
-    def render(self, h, cam, settings, W, H, first=1, stride=1, n=1, strict=True, rtl=True, flat=False, acc=None, steps=None, steps5=None):
-        """steps: None, or the node format (0 compressed / 1 expanded) for the phased kernel's step functions."""
+    def render(self, h, cam, settings, W, H, first=1, stride=1, n=1, strict=True, rtl=True, flat=False, acc=None, steps=None, steps5=None,
+               ext=False):
+        """steps: None, or the node format (0 compressed / 1 expanded) for the phased kernel's step functions.
+        ext: the extended material branch (DRT_FLAG_EXTENDED_MATERIALS)."""
         if acc is None:
             acc = np.zeros(W * H * 3, np.float32)
         cnt = (ctypes.c_ulonglong * 8)()
+        if ext:
+            self.L.emu_render_ext(h, P(cam), P(settings), W, H, first, stride, n, int(strict), int(rtl), P(acc), cnt)
+            return acc, list(cnt)
         if steps5 is not None:
             fmt, nodes_first = steps5
             self.L.emu_render_steps5(h, P(cam), P(settings), W, H, first, stride, n, int(strict), int(rtl), int(fmt), int(nodes_first), P(acc), cnt)
