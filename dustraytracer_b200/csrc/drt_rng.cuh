@@ -25,13 +25,23 @@ DRT_HD float random_float(uint32_t& seed)
 // Random.cu:42-48 draws the three components as ARGUMENTS of make_float3, whose evaluation order the
 // language leaves open: nvcc device code evaluates them left to right, g++ (the host-compiled oracle)
 // right to left. `rtl` selects the oracle's order so that parity runs see the identical stream.
+// randomFloat(seed) * 2 - 1. Production mode folds the exact scalings into one fused multiply-add.
+template <bool STRICT>
+DRT_HD float random_signed(uint32_t& seed)
+{
+	typedef M<STRICT> m;
+	if (STRICT) return m::sub(m::mul(random_float(seed), 2.f), 1.f);
+	seed = pcg_hash(seed);
+	return fmaf((float)seed, 4.6566128730773926e-10f, -1.f);
+}
+
 template <bool STRICT>
 DRT_HD V3 random_unit_vec3(uint32_t& seed, bool rtl)
 {
 	typedef M<STRICT> m;
-	float a = m::sub(m::mul(random_float(seed), 2.f), 1.f);
-	float b = m::sub(m::mul(random_float(seed), 2.f), 1.f);
-	float c = m::sub(m::mul(random_float(seed), 2.f), 1.f);
+	float a = random_signed<STRICT>(seed);
+	float b = random_signed<STRICT>(seed);
+	float c = random_signed<STRICT>(seed);
 	V3 v = rtl ? mk3(c, b, a) : mk3(a, b, c);
 	return m::normalize(v);
 }
@@ -43,8 +53,11 @@ DRT_HD V3 random_unit_sphere_vec3(uint32_t& seed, bool rtl)
 	typedef M<STRICT> m;
 	for (;;) {
 		V3 p = random_unit_vec3<STRICT>(seed, rtl);
-		float len = m::length(p);
-		if (m::mul(len, len) < 1.f) return p;
+		if (STRICT) {
+			float len = m::length(p);
+			if (m::mul(len, len) < 1.f) return p;
+		}
+		else if (m::dot(p, p) < 1.f) return p; // with a correctly rounded sqrt, sqrt(x)^2 < 1 <=> x < 1: no MUFU.SQRT needed
 	}
 }
 
