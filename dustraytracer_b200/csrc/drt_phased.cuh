@@ -425,7 +425,8 @@ DRT_HD bool shade_step(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, 
 			const drt_f4 s0 = ld_f4(sc.shade + 3 * (size_t)hit.prim);
 			V3 fn = mk3(s0.x, s0.y, s0.z);
 			const V3 pos = m::add3(S.o, m::scale(S.d, hit.t));
-			if (m::dot(fn, m::normalize(S.d)) > 0.f) fn = m::scale(fn, -1.f); // ClosestHit.cuh:17-25
+			// ClosestHit.cuh:17-25 flips against normalize(d); the sign does not need the normalisation (production mode)
+			if ((STRICT ? m::dot(fn, m::normalize(S.d)) : m::dot(fn, S.d)) > 0.f) fn = m::scale(fn, -1.f);
 			S.fn = fn;
 			S.o = m::add3(pos, m::scale(fn, 0.001f));                          // RayGen.cuh:121
 			if (SP.enable_sunlight) {
