@@ -351,9 +351,9 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 		return cudaGetLastError();
 	}
 	if (variant >= 2 && P.shade.render_mode != DRT_RENDER_NORMAL) variant = 1;
-	if ((variant == 2 || (variant >= 4 && variant <= 6)) && P.scene.nodes_f32 == nullptr) variant = threads == 128 ? 7 : 3;
-	if (variant >= 7 && threads != 128) variant = 3;
-	if (variant >= 4 && variant <= 6 && threads != 128) variant = 2;
+	if ((variant == 2 || (variant >= 4 && variant <= 6)) && P.scene.nodes_f32 == nullptr) variant = threads <= 128 ? 7 : 3;
+	if (variant >= 7 && threads > 128) variant = 3;
+	if (variant >= 4 && variant <= 6 && threads > 128) variant = 2;
 	if (variant == 7) k_render<STRICT, STATS, 7><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else if (variant == 8) k_render<STRICT, STATS, 8><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else

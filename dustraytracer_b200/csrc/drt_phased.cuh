@@ -509,7 +509,7 @@ struct alignas(16) PermuteLut {
 };
 __device__ const PermuteLut g_permute_lut{};
 
-// Blocks have >= 128 threads: thread i < 128 moves 16 bytes. The load is issued first and the store + barrier come
+// Thread i < 128 moves 16 bytes (smaller blocks loop over the rest at the store). The load is issued first and the store + barrier come
 // after the first camera ray has been set up, so that a one-sample launch does not wait for the table.
 __device__ __forceinline__ uint4 permute_lut_load()
 {
@@ -518,6 +518,8 @@ __device__ __forceinline__ uint4 permute_lut_load()
 __device__ __forceinline__ void permute_lut_store(uint8_t* lut, uint4 v)
 {
 	if (threadIdx.x < DRT_PERMUTE_LUT_BYTES / 16) ((uint4*)lut)[threadIdx.x] = v;
+	for (int i = threadIdx.x + blockDim.x; i < DRT_PERMUTE_LUT_BYTES / 16; i += blockDim.x) // blocks of fewer than 128 threads
+		((uint4*)lut)[i] = __ldg((const uint4*)g_permute_lut.v + i);
 	__syncthreads();
 }
 

@@ -96,6 +96,7 @@ def main():
     ap.add_argument("--spp-scale", type=float, default=1.0)
     ap.add_argument("--ref-frames", type=int, default=4)
     ap.add_argument("--variant", type=int, default=-1)
+    ap.add_argument("--block", type=int, default=0, help="threads per block (0 = default)")
     a = ap.parse_args()
     import oracles as O
     for key in a.configs.split(","):
@@ -123,8 +124,8 @@ def main():
         del rs
         r = drt.Renderer()
         r.m_RendererSettings = settings
-        if a.variant >= 0:
-            r.set_tuning(a.variant, 0)
+        if a.variant >= 0 or a.block:
+            r.set_tuning(a.variant if a.variant >= 0 else 4, a.block)
         r.ResizeBuffer(W, H)
         r.Render(cam, scene, min(spp, 2))  # warm-up
         r.resetAccumulationBuffer()
