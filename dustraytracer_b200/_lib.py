@@ -45,7 +45,8 @@ class drt_bvh_params(ctypes.Structure):
 class drt_scene_stats(ctypes.Structure):
     _fields_ = [(n, ctypes.c_uint64) for n in
                 ("triangles", "materials", "textures", "meshes", "wide_nodes", "bvh2_nodes", "bvh_levels", "device_bytes")] + \
-               [("build_ms", ctypes.c_double), ("load_ms", ctypes.c_double)]
+               [("build_ms", ctypes.c_double), ("load_ms", ctypes.c_double)] + \
+               [(n, ctypes.c_uint64) for n in ("alpha_tris", "alpha_opaque", "alpha_hidden")]
 
 
 class drt_hit(ctypes.Structure):

@@ -112,8 +112,9 @@ class Scene:
         h, w, c = px.shape
         check(_lib.lib().drt_scene_add_texture(self._h, w, h, c, px.ctypes.data))
 
-    def build_bvh(self, device=0, bin_count=8, leaf_target=20):
+    def build_bvh(self, device=0, bin_count=8, leaf_target=20, classify_alpha=True):
         p = drt_bvh_params(bin_count=bin_count, leaf_target=leaf_target)
+        p.reserved[0] = 0 if classify_alpha else 1
         check(_lib.lib().drt_scene_build_bvh(self._h, ctypes.byref(p), device))
 
     def stats(self):

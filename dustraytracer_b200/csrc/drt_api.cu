@@ -140,6 +140,14 @@ static void fill_stats(drt_scene* s)
 	s->stats.materials = s->host.materials.size();
 	s->stats.textures = s->host.textures.size();
 	s->stats.meshes = s->host.meshes;
+	std::vector<uint8_t> cls; // host-only: what the build will do with the alpha-tested triangles
+	classify_alpha_triangles(s->host, cls);
+	s->stats.alpha_tris = s->stats.alpha_opaque = s->stats.alpha_hidden = 0;
+	for (uint8_t c : cls) {
+		if (c != ALPHA_NONE) s->stats.alpha_tris++;
+		if (c == ALPHA_OPAQUE) s->stats.alpha_opaque++;
+		if (c == ALPHA_HIDDEN) s->stats.alpha_hidden++;
+	}
 }
 
 extern "C" {
@@ -267,8 +275,9 @@ int drt_scene_get_texture(const drt_scene* scene, int32_t index, int32_t* width,
 // ---------------------------------------------------------------------------------------------
 // scene upload + GPU build
 // ---------------------------------------------------------------------------------------------
-extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* /*params_or_null*/, int device)
+extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* params_or_null, int device)
 {
+	const bool classify_alpha = !(params_or_null && (params_or_null->reserved[0] & 1));
 	if (!scene) return fail(DRT_ERR_INVALID, "drt_scene_build_bvh: null scene");
 	int ndev = 0;
 	DRT_CUDA(cudaGetDeviceCount(&ndev));
@@ -324,6 +333,20 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* /*par
 		}
 		mat_word[i] = (int32_t)((uint32_t)mi | flag);
 	}
+	// exact opacity classification (drt_host.h): triangles that can never fail the alpha test lose the flag, triangles
+	// that can never pass it are collapsed to a point for the build (a degenerate triangle is rejected by Moller-Trumbore)
+	std::vector<float> pos_build;
+	if (classify_alpha) {
+		std::vector<uint8_t> cls;
+		classify_alpha_triangles(h, cls);
+		for (size_t i = 0; i < n; i++) {
+			if (cls[i] == ALPHA_OPAQUE) mat_word[i] &= 0x7fffffff;
+			else if (cls[i] == ALPHA_HIDDEN) {
+				if (pos_build.empty()) pos_build = h.pos;
+				for (int k = 1; k < 3; k++) for (int c = 0; c < 3; c++) pos_build[9 * i + 3 * k + c] = pos_build[9 * i + c];
+			}
+		}
+	}
 	DRT_CUDA(scene->texdesc.alloc(texdesc.size() ? texdesc.size() : 1));
 	DRT_CUDA(scene->texels.alloc(texels.size() ? texels.size() : 1));
 	DRT_CUDA(scene->materials.alloc(mats.size()));
@@ -354,7 +377,7 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* /*par
 		DRT_CUDA(bins.alloc(build_bin_slots_capacity((int)n) * 3 * DRT_BINS * DRT_BIN_WORDS));
 		DRT_CUDA(wide_src.alloc(n + 1)); DRT_CUDA(wide_tmp.alloc(n + 1));
 		DRT_CUDA(scene->tris.alloc(3 * n)); DRT_CUDA(scene->shade.alloc(3 * n));
-		DRT_CUDA(cudaMemcpyAsync(d_pos.p, h.pos.data(), 9 * n * 4, cudaMemcpyHostToDevice, stream));
+		DRT_CUDA(cudaMemcpyAsync(d_pos.p, pos_build.empty() ? h.pos.data() : pos_build.data(), 9 * n * 4, cudaMemcpyHostToDevice, stream));
 		DRT_CUDA(cudaMemcpyAsync(d_uv.p, h.uv.data(), 6 * n * 4, cudaMemcpyHostToDevice, stream));
 		DRT_CUDA(cudaMemcpyAsync(d_fn.p, h.fnormal.data(), 3 * n * 4, cudaMemcpyHostToDevice, stream));
 		DRT_CUDA(cudaMemcpyAsync(d_mat.p, mat_word.data(), n * 4, cudaMemcpyHostToDevice, stream));

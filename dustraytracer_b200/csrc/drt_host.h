@@ -1,6 +1,7 @@
 // drt_host.h -- host-side scene representation shared by the loader, the uploader and the C ABI.
 #pragma once
 #include <stdint.h>
+#include <math.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -49,6 +50,76 @@ inline void fill_materials_ext(const std::vector<drt_material>& mats, std::vecto
 		o[4] = mats[i].roughness; o[5] = mats[i].refractive_index;
 	}
 	out8[8 * mats.size() + 5] = 1.45f;
+}
+
+// Opacity classification of alpha-tested triangles (host side, exact). The device accepts a hit on a triangle whose
+// albedo texture has 4 components only if the nearest texel at the interpolated UV has alpha 255 (AnyHit.cuh:17-25;
+// drt_trace.cuh alpha_accept). The texels a triangle can ever sample lie in the bounding box of its three UVs in texel
+// space (barycentrics of accepted hits are a convex combination; padded by one texel for rounding and for the
+// reference's row overrun at frac() == 1). If every texel of that box has alpha 255 the test can never fail
+// (class OPAQUE: skip it); if none has, the triangle can never be hit (class HIDDEN). Counted with a summed-area table
+// per RGBA texture. Results are bit-identical with and without the classification.
+enum { ALPHA_NONE = 0, ALPHA_TEST = 1, ALPHA_OPAQUE = 2, ALPHA_HIDDEN = 3 };
+inline void classify_alpha_triangles(const HostScene& h, std::vector<uint8_t>& cls)
+{
+	const size_t n = h.tri_count(), nm = h.materials.size();
+	cls.assign(n, (uint8_t)ALPHA_NONE);
+	std::vector<std::vector<uint32_t>> sat(h.textures.size()); // (H+1) x (W+1) counts of alpha < 255
+	auto table = [&](int ti) -> const std::vector<uint32_t>& {
+		std::vector<uint32_t>& s = sat[ti];
+		if (s.empty()) {
+			const HostTexture& t = h.textures[ti];
+			const size_t W = (size_t)t.width, H = (size_t)t.height;
+			s.assign((H + 1) * (W + 1), 0u);
+			for (size_t y = 0; y < H; y++) {
+				uint32_t row = 0;
+				for (size_t x = 0; x < W; x++) {
+					row += t.pixels[(y * W + x) * 4 + 3] < 255 ? 1u : 0u;
+					s[(y + 1) * (W + 1) + x + 1] = s[y * (W + 1) + x + 1] + row;
+				}
+			}
+		}
+		return s;
+	};
+	for (size_t i = 0; i < n; i++) {
+		const int mi = h.mat[i];
+		if (mi < 0 || (size_t)mi >= nm) continue;
+		const int ti = h.materials[mi].albedo_texture_index;
+		if (ti < 0 || ti >= (int)h.textures.size() || h.textures[ti].comps != 4) continue;
+		cls[i] = (uint8_t)ALPHA_TEST;
+		const HostTexture& t = h.textures[ti];
+		const long long W = t.width, H = t.height;
+		if (W <= 2 || H <= 2) continue;
+		const float* uv = &h.uv[6 * i];
+		float umin = uv[0], umax = uv[0], vmin = uv[1], vmax = uv[1];
+		bool ok = true;
+		for (int k = 0; k < 3; k++) {
+			const float u = uv[2 * k], v = uv[2 * k + 1];
+			if (!(u == u) || !(v == v) || u > 64.f || u < -64.f || v > 64.f || v < -64.f) ok = false; // rounding of huge UVs: do not reason
+			umin = u < umin ? u : umin; umax = u > umax ? u : umax;
+			vmin = v < vmin ? v : vmin; vmax = v > vmax ? v : vmax;
+		}
+		if (!ok) continue;
+		const long long x0 = (long long)floor((double)umin * W) - 1, x1 = (long long)floor((double)umax * W) + 1;
+		const long long y0 = (long long)floor((double)vmin * H) - 1, y1 = (long long)floor((double)vmax * H) + 1;
+		if (x1 - x0 + 1 >= W || y1 - y0 + 1 >= H) continue; // wraps around the whole texture
+		const std::vector<uint32_t>& s = table(ti);
+		auto rect = [&](long long ax, long long bx, long long ay, long long by) -> uint64_t { // inclusive, inside the texture
+			const size_t P = (size_t)W + 1;
+			return (uint64_t)s[(size_t)(by + 1) * P + (size_t)(bx + 1)] - s[(size_t)ay * P + (size_t)(bx + 1)]
+				- s[(size_t)(by + 1) * P + (size_t)ax] + s[(size_t)ay * P + (size_t)ax];
+		};
+		auto wrap = [](long long a, long long m) { long long r = a % m; return r < 0 ? r + m : r; };
+		long long xs[2][2], ys[2][2];
+		int nx = 1, ny = 1;
+		{ const long long a = wrap(x0, W), b = wrap(x1, W); if (a <= b) { xs[0][0] = a; xs[0][1] = b; } else { xs[0][0] = a; xs[0][1] = W - 1; xs[1][0] = 0; xs[1][1] = b; nx = 2; } }
+		{ const long long a = wrap(y0, H), b = wrap(y1, H); if (a <= b) { ys[0][0] = a; ys[0][1] = b; } else { ys[0][0] = a; ys[0][1] = H - 1; ys[1][0] = 0; ys[1][1] = b; ny = 2; } }
+		uint64_t holes = 0;
+		for (int a = 0; a < nx; a++) for (int b = 0; b < ny; b++) holes += rect(xs[a][0], xs[a][1], ys[b][0], ys[b][1]);
+		const uint64_t area = (uint64_t)(x1 - x0 + 1) * (uint64_t)(y1 - y0 + 1);
+		if (holes == 0) cls[i] = (uint8_t)ALPHA_OPAQUE;
+		else if (holes == area) cls[i] = (uint8_t)ALPHA_HIDDEN;
+	}
 }
 
 void set_error(const std::string& msg);

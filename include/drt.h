@@ -77,7 +77,7 @@ typedef struct drt_material {
 typedef struct drt_bvh_params {
 	int32_t bin_count;   /* informational: the GPU builder uses 16 bins (8 for small nodes); ref m_BinCount = 8 */
 	int32_t leaf_target; /* informational: wide-node leaf slots hold <= 3 triangles; ref m_TargetLeafPrimitivesCount */
-	int32_t reserved[6];
+	int32_t reserved[6]; /* reserved[0] bit 0: disable the opacity classification of alpha-tested triangles (A/B checks) */
 } drt_bvh_params;
 
 typedef struct drt_scene_stats {
@@ -86,6 +86,9 @@ typedef struct drt_scene_stats {
 	uint64_t device_bytes;   /* nodes + triangles + shading records + textures resident in HBM */
 	double build_ms;         /* device time of the last drt_scene_build_bvh */
 	double load_ms;
+	/* alpha-tested triangles (albedo texture with 4 components, AnyHit.cuh:17), and how many of them the exact host-side
+	 * opacity classification proved always-opaque (test skipped) / never-hittable (collapsed); set by drt_scene_build_bvh */
+	uint64_t alpha_tris, alpha_opaque, alpha_hidden;
 } drt_scene_stats;
 
 typedef struct drt_hit {

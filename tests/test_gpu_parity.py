@@ -364,3 +364,33 @@ def test_debug_views_bit_exact(drt, name):
     heat = r.readback(drt.DRT_ACCUM_RGB32F)
     assert np.isfinite(heat).all() and heat.max() > 0.05
     orc.free(oh)
+
+
+@pytest.mark.parametrize("name", ["animemaid", "mc_transparency_test"])
+def test_opacity_classification_changes_nothing_but_the_work(drt, name):
+    """Alpha-tested triangles proven always-opaque skip the test, never-hittable ones are collapsed (drt_host.h): the
+    images, hit ids and ray counts are bit-identical with the classification on and off; only the number of alpha
+    tests drops."""
+    W, H, spp = 320, 180, 8
+    out = []
+    for on in (True, False):
+        s = drt.Scene()
+        s.loadGLTFmodel(O.scene_path(name))
+        s.build_bvh(classify_alpha=on)
+        r = drt.Renderer(flags=STRICT | drt.DRT_FLAG_STATS)
+        r.m_RendererSettings = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=4, max_samples=1 << 20)
+        r.ResizeBuffer(W, H)
+        hits = r.trace_primary(drt.Camera(), s, 1)
+        r.counters(reset=True)
+        r.Render(drt.Camera(), s, spp)
+        out.append((hits, r.readback(drt.DRT_ACCUM_RGB32F), r.counters(), s.stats()))
+    (h1, a1, c1, st1), (h0, a0, c0, st0) = out
+    for k in ("prim_id", "t", "u", "v"):
+        assert np.array_equal(bits(h1[k]), bits(h0[k]))
+    assert np.array_equal(bits(a1), bits(a0))
+    assert c1["closest_rays"] == c0["closest_rays"] and c1["shadow_rays"] == c0["shadow_rays"]
+    print("%s: alpha tests %d -> %d (%d of %d alpha-tested triangles proven opaque, %d hidden)"
+          % (name, c0["alpha_tests"], c1["alpha_tests"], st1["alpha_opaque"], st1["alpha_tris"], st1["alpha_hidden"]))
+    assert c1["alpha_tests"] <= c0["alpha_tests"]
+    if name == "animemaid":
+        assert c1["alpha_tests"] < 0.9 * c0["alpha_tests"]
