@@ -1,0 +1,44 @@
+#!/usr/bin/env python3
+"""The reference's call pattern: Renderer::Render once per displayed frame = ONE sample per launch (Renderer.cu:80-117).
+Times N such calls through the C ABI (wall clock, each call returns with the frame complete) next to one batched call,
+and the reference's own CUDA path launched the same way."""
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import dustraytracer_b200 as drt  # noqa: E402
+import bench  # noqa: E402
+
+N = 256
+scene = drt.Scene()
+scene.loadGLTFmodel(bench.SCENE_PATH)
+drt.BVHBuilder().buildIterative(scene)
+r = drt.Renderer()
+r.m_RendererSettings = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=8, max_samples=1 << 30)
+r.ResizeBuffer(1920, 1080)
+cam = drt.Camera()
+for _ in range(8):
+    r.Render(cam, scene)
+r.resetAccumulationBuffer()
+r.counters(reset=True)
+t0 = time.perf_counter()
+dev_ms = 0.0
+for _ in range(N):
+    dev_ms += r.Render(cam, scene)
+wall = time.perf_counter() - t0
+c = r.counters(reset=True)
+rays = c["closest_rays"] + c["shadow_rays"]
+r.resetAccumulationBuffer()
+t0 = time.perf_counter()
+ms_b = r.Render(cam, scene, N)
+wall_b = time.perf_counter() - t0
+bench.claim_stdout()
+ref = bench.ref_cuda_baseline(frames=64)
+bench.emit_json_line({"scene": "room.glb 1920x1080, 8 bounces, sun", "calls": N,
+                      "one_sample_per_call": {"wall_ms_per_sample": wall / N * 1e3, "device_ms_per_sample": dev_ms / N, "Mrays_s_wall": rays / wall / 1e6},
+                      "one_batched_call": {"wall_ms_per_sample": wall_b / N * 1e3, "device_ms_per_sample": ms_b / N},
+                      "reference_cuda_one_sample_per_launch_ms": {k: v["ms_per_sample"] for k, v in (ref or {}).items()}})
