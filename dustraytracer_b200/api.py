@@ -220,7 +220,7 @@ class Renderer:
     def set_flags(self, flags):
         check(_lib.lib().drt_renderer_set_flags(self._h, flags))
 
-    def set_tuning(self, variant=0, block_threads=0):
+    def set_tuning(self, variant=-1, block_threads=0):
         check(_lib.lib().drt_renderer_set_tuning(self._h, variant, block_threads))
 
     def set_stream(self, cuda_stream_ptr):

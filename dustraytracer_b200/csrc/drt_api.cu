@@ -123,6 +123,7 @@ struct drt_renderer {
 	uint32_t width = 0, height = 0;
 	DevBuf<drt_f4> accum, display;
 	DevBuf<Counters> counters;
+	DevBuf<unsigned> work_queue; // pixel-queue kernel: next tile, warps that have left (the kernel leaves both at zero)
 	DevBuf<Hit> hits;
 	DevBuf<uint8_t> staging;
 	uint32_t frame_index = 1;   // the reference's m_FrameIndex (Renderer.hpp:41): next frame to render
@@ -130,7 +131,24 @@ struct drt_renderer {
 	uint32_t first_frame = 1, stride = 1;
 	uint32_t flags = 0;
 	int variant = 4, block_threads = 0;
+	bool auto_variant = true; // no explicit drt_renderer_set_tuning: the launch auto-tuner may pick the kernel
 	int sched_bias[3] = { 0, 0, 0 };
+	// Launches of at most queue_max_spp samples (the reference's interactive pattern is ONE per launch) may run the
+	// persistent pixel-queue kernel (variant 9) instead of the fixed-pixel kernel (variant 4). Both give the same bits, and
+	// which is faster depends on the view (room.glb 1.38x, sky-dominated dense_monkey.glb 0.82x), so the renderer MEASURES:
+	// for a new (scene, size, samples, settings) it times each candidate twice with the launch's own events, keeps the
+	// fastest and probes again every DRT_AUTOTUNE_PERIOD launches.
+	int queue_max_spp = DRT_QUEUE_MAX_SPP_DEFAULT;
+	struct AutoTune {
+		const void* scene = nullptr;
+		uint32_t w = 0, h = 0, n = 0, flags = 0;
+		int32_t bounce = -1, sun = -1;
+		int step = 0;                          // < 2 * candidates: probing candidate step % candidates
+		float best_ms[3] = { 0.f, 0.f, 0.f };
+		int choice = 0;
+		int settled_launches = 0;
+	} tune;
+	int sm_count = 0;
 	int kernel_launches = 0;
 };
 
@@ -481,9 +499,13 @@ extern "C" int drt_renderer_create(int device, drt_renderer** out)
 	if (e == cudaSuccess) e = cudaEventCreate(&r->ev1);
 	if (e == cudaSuccess) e = r->counters.alloc(1);
 	if (e == cudaSuccess) e = cudaMemset(r->counters.p, 0, sizeof(Counters));
+	if (e == cudaSuccess) e = r->work_queue.alloc(2);
+	if (e == cudaSuccess) e = cudaMemsetAsync(r->work_queue.p, 0, 2 * sizeof(unsigned), r->own_stream);
+	if (e == cudaSuccess) e = cudaDeviceGetAttribute(&r->sm_count, cudaDevAttrMultiProcessorCount, device);
 	if (e != cudaSuccess) { delete r; return fail(DRT_ERR_CUDA, std::string("drt_renderer_create: ") + cudaGetErrorString(e)); }
 	r->stream = r->own_stream;
 	if (const char* b = getenv("DRT_SCHED_BIAS")) sscanf(b, "%d,%d,%d", &r->sched_bias[0], &r->sched_bias[1], &r->sched_bias[2]); // measurement knob
+	if (const char* b = getenv("DRT_QUEUE_MAX_SPP")) r->queue_max_spp = atoi(b);                                                   // measurement knob
 	*out = r;
 	return DRT_OK;
 }
@@ -518,8 +540,9 @@ extern "C" int drt_renderer_set_flags(drt_renderer* r, uint32_t flags)
 extern "C" int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads)
 {
 	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: null renderer");
-	if (variant < 0 || variant > 8 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
-	r->variant = variant; r->block_threads = block_threads;
+	if (variant < -1 || variant > 14 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
+	r->auto_variant = variant < 0;
+	r->variant = variant < 0 ? 4 : variant; r->block_threads = block_threads;
 	return DRT_OK;
 }
 
@@ -577,7 +600,51 @@ static int make_render_params(drt_renderer* r, const drt_camera* cam, const drt_
 	P.shade = make_shade_params(*settings);
 	P.width = (int32_t)r->width; P.height = (int32_t)r->height;
 	P.accum = r->accum.p; P.display = r->display.p; P.counters = r->counters.p;
+	P.work_queue = r->work_queue.p;
 	return DRT_OK;
+}
+
+#define DRT_AUTOTUNE_CANDIDATES 3
+#define DRT_AUTOTUNE_PERIOD 256
+
+// Candidate c of the launch auto-tuner: 0 = fixed-pixel kernel, 1 / 2 = pixel-queue kernel with an early / late refill.
+static void autotune_apply(int c, uint32_t n, LaunchConfig& cfg)
+{
+	if (c == 0) return;
+	cfg.variant = 9;
+	cfg.sched_bias[1] = c == 1 ? 4 : (n <= 1 ? 16 : 10);
+}
+
+// Returns the candidate this launch runs (and whether its time is a probe), or -1 when the launch is not eligible.
+static int autotune_pick(drt_renderer* r, const drt_scene* scene, const RenderParams& P, bool& probing)
+{
+	probing = false;
+	if (!r->auto_variant || r->variant != 4 || (r->block_threads != 0 && r->block_threads != 128) || r->sched_bias[1] != 0 || (int64_t)P.n_samples > (int64_t)r->queue_max_spp) return -1;
+	if (P.shade.render_mode != 0 || (r->flags & DRT_FLAG_EXTENDED_MATERIALS) || P.width >= 65536 || P.height >= 65536) return -1;
+	drt_renderer::AutoTune& t = r->tune;
+	if (t.scene != scene || t.w != (uint32_t)P.width || t.h != (uint32_t)P.height || t.n != P.n_samples || t.flags != r->flags ||
+		t.bounce != P.shade.bounce_limit || t.sun != P.shade.enable_sunlight) {
+		t = drt_renderer::AutoTune();
+		t.scene = scene; t.w = (uint32_t)P.width; t.h = (uint32_t)P.height; t.n = P.n_samples; t.flags = r->flags;
+		t.bounce = P.shade.bounce_limit; t.sun = P.shade.enable_sunlight;
+	}
+	if (t.step < 2 * DRT_AUTOTUNE_CANDIDATES) { probing = true; return t.step % DRT_AUTOTUNE_CANDIDATES; }
+	return t.choice;
+}
+
+static void autotune_record(drt_renderer* r, int candidate, bool probing, float ms)
+{
+	drt_renderer::AutoTune& t = r->tune;
+	if (!probing) {
+		if (++t.settled_launches >= DRT_AUTOTUNE_PERIOD) { t.step = 0; t.settled_launches = 0; }
+		return;
+	}
+	if (t.step < DRT_AUTOTUNE_CANDIDATES || ms < t.best_ms[candidate]) t.best_ms[candidate] = ms;
+	if (++t.step == 2 * DRT_AUTOTUNE_CANDIDATES) {
+		t.choice = 0;
+		for (int c = 1; c < DRT_AUTOTUNE_CANDIDATES; c++)
+			if (t.best_ms[c] < 0.98f * t.best_ms[t.choice]) t.choice = c; // the fixed-pixel kernel keeps ties
+	}
 }
 
 static LaunchConfig launch_config(const drt_renderer* r)
@@ -588,6 +655,7 @@ static LaunchConfig launch_config(const drt_renderer* r)
 	cfg.stats = (r->flags & DRT_FLAG_STATS) != 0;
 	cfg.ext_materials = (r->flags & DRT_FLAG_EXTENDED_MATERIALS) != 0;
 	cfg.variant = r->variant; cfg.block_threads = r->block_threads;
+	cfg.resident_sms = r->sm_count;
 	for (int i = 0; i < 3; i++) cfg.sched_bias[i] = r->sched_bias[i];
 	return cfg;
 }
@@ -618,11 +686,18 @@ extern "C" int drt_renderer_render(drt_renderer* r, const drt_camera* cam, const
 	P.frame_stride = r->stride;
 	P.n_samples = n;
 	P.total_samples = (float)(r->samples_done + n); // = the frame index the reference divides by (RenderKernel.cu:30)
+	LaunchConfig cfg = launch_config(r);
+	bool probing = false;
+	const int candidate = autotune_pick(r, scene, P, probing);
+	if (candidate >= 0) autotune_apply(candidate, n, cfg);
 	DRT_CUDA(cudaEventRecord(r->ev0, r->stream));
-	DRT_CUDA(launch_render(P, launch_config(r), r->stream, &r->kernel_launches));
+	DRT_CUDA(launch_render(P, cfg, r->stream, &r->kernel_launches));
 	DRT_CUDA(cudaEventRecord(r->ev1, r->stream));
 	DRT_CUDA(cudaEventSynchronize(r->ev1)); // like Renderer.cu:105-106 the call returns with the frame done
-	if (ms_or_null) DRT_CUDA(cudaEventElapsedTime(ms_or_null, r->ev0, r->ev1));
+	float ms = 0.f;
+	if (ms_or_null || candidate >= 0) DRT_CUDA(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+	if (ms_or_null) *ms_or_null = ms;
+	if (candidate >= 0) autotune_record(r, candidate, probing, ms);
 	r->samples_done += n;
 	r->frame_index += n;
 	return DRT_OK;

@@ -104,6 +104,46 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 	flush_counters(P.counters, pc, st);
 }
 
+// Phased kernel with the SHADE-only lane state in shared memory (drt_phased.cuh render_warp_cold).
+//   CV 0 / 1 / 2 : fixed pixel per lane, expanded fp32 nodes, 8 / 7 / 6 resident blocks per SM   (variants 11 / 12 / 13)
+//   CV 5         : fixed pixel per lane, compressed nodes, 8 blocks per SM                        (variant 14)
+//   CV 3 / 4     : persistent pixel-queue kernel, fp32 / compressed nodes, 8 blocks per SM        (variants 9 / 10):
+//                  grid = resident blocks of the device, warps pull 8x4 tiles from P.work_queue[0]; the last warp to
+//                  leave resets the queue words for the next launch.
+template <bool STRICT, bool STATS, int CV>
+__global__ void __launch_bounds__(128, (CV == 1 || CV == 3 || CV == 4) ? 7 : (CV == 2 ? 6 : 8)) k_render_cold(const __grid_constant__ RenderParams P, const bool rtl, const PhasedTuning tune)
+{
+	constexpr bool QUEUE = CV == 3 || CV == 4;
+	constexpr int FMT = (CV == 4 || CV == 5) ? NODE_FMT_Q8 : NODE_FMT_F32;
+	TraceStats ts;
+	ts.nodes = ts.tris = ts.ties = ts.alpha = ts.max_stack = ts.clamps = 0;
+	TraceStats* st = STATS ? &ts : nullptr;
+	__shared__ alignas(16) uint8_t lut[DRT_PERMUTE_LUT_BYTES];
+	__shared__ uint32_t cold[DRT_COLD_WORDS];
+	int x = 0, y = 0;
+	bool valid = false;
+	if (!QUEUE) pixel_of_thread(P.width, P.height, 4, x, y, valid);
+	render_warp_cold<STRICT, STATS, FMT, QUEUE>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, st, lut, cold);
+	const uint32_t* c = cold + threadIdx.x;
+	if (!QUEUE && valid) {
+		const size_t p = (size_t)x + (size_t)y * (size_t)P.width;
+		const V3 acc = cold_get3(c, CF_ACC);
+		P.accum[p] = make_float4(acc.x, acc.y, acc.z, 0.f);
+		P.display[p] = make_float4(acc.x / P.total_samples, acc.y / P.total_samples, acc.z / P.total_samples, 1.f);
+	}
+	PathCounters pc;
+	pc.closest = c[CF_CLOSEST * DRT_COLD_THREADS]; pc.shadow = c[CF_SHADOW * DRT_COLD_THREADS];
+	flush_counters(P.counters, pc, st);
+	if (QUEUE && (threadIdx.x & 31) == 0) {
+		__threadfence();
+		const unsigned warps = gridDim.x * (blockDim.x >> 5);
+		if (atomicAdd(P.work_queue + 1, 1u) == warps - 1u) {
+			P.work_queue[0] = 0u;
+			P.work_queue[1] = 0u;
+		}
+	}
+}
+
 template <bool STRICT>
 __global__ void __launch_bounds__(256) k_trace_primary(const __grid_constant__ RenderParams P, const uint32_t frameidx, Hit* out,
 	const bool rtl, const int warps_per_block)
@@ -344,6 +384,7 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	const unsigned blocks = (unsigned)((tiles + wpb - 1) / wpb);
 	PhasedTuning tune;
 	tune.stick = cfg.sched_bias[0] > 0 ? cfg.sched_bias[0] : 6; // measured: room best at 8, dense_monkey at 4 (33 = never)
+	tune.refill = cfg.sched_bias[1] > 0 ? cfg.sched_bias[1] : (P.n_samples <= 1 ? 12 : (P.n_samples <= 4 ? 6 : 1));
 	// the phased kernels implement NORMALMODE; the debug views go through the reference-shaped loop
 	int variant = cfg.variant;
 	if (cfg.ext_materials && P.shade.render_mode == DRT_RENDER_NORMAL) {
@@ -351,6 +392,37 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 		return cudaGetLastError();
 	}
 	if (variant >= 2 && P.shade.render_mode != DRT_RENDER_NORMAL) variant = 1;
+	// variants 9 / 10: persistent warps with a pixel queue, for launches of few samples (the reference's interactive pattern is
+	// one per launch); the renderer's auto-tuner (drt_api.cu) picks between them and variant 4 by measurement.
+	if (variant >= 9 && variant <= 14) {
+		const bool queue = variant <= 10;
+		const bool ok = threads == 128 && P.width < 65536 && P.height < 65536 && (!queue || (P.work_queue != nullptr && cfg.resident_sms > 0));
+		const bool q8 = variant == 10 || variant == 14 || P.scene.nodes_f32 == nullptr;
+		if (!ok) variant = q8 ? 7 : 4;
+		else if (queue) {
+			// persistent grid = what is resident at once (asked from the runtime: a block that had to wait would find the queue empty)
+			static int per_sm[2] = { 0, 0 };
+			if (per_sm[q8 ? 1 : 0] == 0) {
+				int nb = 0;
+				const cudaError_t oe = q8 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_render_cold<STRICT, STATS, 4>, threads, 0)
+				                          : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_render_cold<STRICT, STATS, 3>, threads, 0);
+				if (oe != cudaSuccess) return oe;
+				per_sm[q8 ? 1 : 0] = nb > 0 ? nb : 1;
+			}
+			long long qblocks = (long long)cfg.resident_sms * per_sm[q8 ? 1 : 0];
+			if (qblocks * wpb > tiles) qblocks = (tiles + wpb - 1) / wpb; // at least one tile per warp
+			if (q8) k_render_cold<STRICT, STATS, 4><<<(unsigned)qblocks, threads, 0, s>>>(P, cfg.rtl, tune);
+			else k_render_cold<STRICT, STATS, 3><<<(unsigned)qblocks, threads, 0, s>>>(P, cfg.rtl, tune);
+			return cudaGetLastError();
+		}
+		else {
+			if (q8) k_render_cold<STRICT, STATS, 5><<<blocks, threads, 0, s>>>(P, cfg.rtl, tune);
+			else if (variant == 12) k_render_cold<STRICT, STATS, 1><<<blocks, threads, 0, s>>>(P, cfg.rtl, tune);
+			else if (variant == 13) k_render_cold<STRICT, STATS, 2><<<blocks, threads, 0, s>>>(P, cfg.rtl, tune);
+			else k_render_cold<STRICT, STATS, 0><<<blocks, threads, 0, s>>>(P, cfg.rtl, tune);
+			return cudaGetLastError();
+		}
+	}
 	if ((variant == 2 || (variant >= 4 && variant <= 6)) && P.scene.nodes_f32 == nullptr) variant = threads <= 128 ? 7 : 3;
 	if (variant >= 7 && threads > 128) variant = 3;
 	if (variant >= 4 && variant <= 6 && threads > 128) variant = 2;

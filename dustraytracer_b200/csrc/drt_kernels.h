@@ -6,6 +6,11 @@
 
 namespace drt {
 
+// Largest launch (samples per pixel) for which the renderer's auto-tuner considers the persistent pixel-queue kernel.
+#ifndef DRT_QUEUE_MAX_SPP_DEFAULT
+#define DRT_QUEUE_MAX_SPP_DEFAULT 8
+#endif
+
 struct LaunchConfig {
 	bool strict = false;  // DRT_FLAG_STRICT
 	bool rtl = false;     // DRT_FLAG_HOST_ARG_ORDER
@@ -14,6 +19,7 @@ struct LaunchConfig {
 	int variant = 4;      // render kernel variant (see drt_kernels.cu); 4 = default
 	int sched_bias[3] = { 0, 0, 0 }; // phased kernels: [0] = sticky re-issue threshold (0 = default 6, 33 = never)
 	int block_threads = 0; // 0 = variant default
+	int resident_sms = 0;  // SM count of the device (grid of the persistent kernel)
 };
 
 cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s);

@@ -489,7 +489,8 @@ DRT_HD V3 render_pixel_steps(const RenderParams& P, uint32_t x, uint32_t y, bool
 #if defined(__CUDACC__)
 // Scheduling weights of the vote (launch parameters so that they can be swept without recompiling).
 struct PhasedTuning {
-	int stick; // a step is re-issued without a full vote while at least this many lanes want it again (33 = never)
+	int stick;  // a step is re-issued without a full vote while at least this many lanes want it again (33 = never)
+	int refill; // pixel-queue kernel: idle lanes take new pixels once at least this many of them wait (1..32)
 };
 
 // The permutation table, constant-initialised in device memory (2 KB, L2/L1 resident), and the per-block copy to
@@ -581,6 +582,186 @@ __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const Ph
 	}
 	return S.acc;
 }
+
+// ---------------------------------------------------------------------------------------------
+// The same loop with the SHADE-only part of the lane state parked in shared memory.
+// light, throughput, normal, pixel sum, RNG state, sample / bounce counters, ray counters and the pixel coordinates
+// (18 words per lane) are dead weight in the registers of the NODE and TRI steps, which issue ~75 % of the
+// instructions. They live in a [field][thread] array of shared memory (conflict-free) and are loaded / stored around
+// the SHADE step; what stays in registers is the ray (o, d, shadow flag), the slab constants and the traversal
+// cursor. That fits 64 registers without spills in the hot steps -> 8 resident blocks per SM instead of 6.
+// QUEUE adds the pixel queue of the persistent kernel (see below); per pixel the arithmetic is unchanged.
+// ---------------------------------------------------------------------------------------------
+enum { CF_LIGHT = 0, CF_THRU = 3, CF_FN = 6, CF_ACC = 9, CF_SEED = 12, CF_K = 13, CF_BOUNCE = 14, CF_CLOSEST = 15, CF_SHADOW = 16, CF_XY = 17, CF_COUNT = 18 };
+#define DRT_COLD_THREADS 128
+#define DRT_COLD_WORDS (CF_COUNT * DRT_COLD_THREADS)
+#define DRT_QUEUE_NO_PIXEL 0xffffffffu
+
+__device__ __forceinline__ void cold_put3(uint32_t* c, int f, V3 v)
+{
+	c[(f + 0) * DRT_COLD_THREADS] = __float_as_uint(v.x); c[(f + 1) * DRT_COLD_THREADS] = __float_as_uint(v.y); c[(f + 2) * DRT_COLD_THREADS] = __float_as_uint(v.z);
+}
+__device__ __forceinline__ V3 cold_get3(const uint32_t* c, int f)
+{
+	return mk3(__uint_as_float(c[(f + 0) * DRT_COLD_THREADS]), __uint_as_float(c[(f + 1) * DRT_COLD_THREADS]), __uint_as_float(c[(f + 2) * DRT_COLD_THREADS]));
+}
+
+// Pixel queue of one persistent warp (warp-uniform registers): the 8x4 tile it is handing out and how many of its pixels
+// are gone. Tiles come from ONE global counter (lane 0, one atomic per 32 pixels).
+struct WarpQueue {
+	unsigned org;    // tile origin, x | y << 16
+	unsigned cursor; // pixels of the tile already handed out (32 = none left)
+	unsigned pending; // lane 0: index of the next tile, requested ahead of its use
+};
+
+// REFILL step (warp-uniform call): the lanes of `idle` take the next pixels of the warp's queue in rank order, load the
+// pixel's sum and start its first sample. Returns false when the queue is empty and the global counter has run out.
+template <bool STRICT>
+__device__ __forceinline__ bool queue_refill(const RenderParams& P, WarpQueue& q, unsigned idle, bool rtl, uint32_t* c,
+	V3& o, V3& d, RayBox& R, LaneTrav& L, int& phase, int first_phase)
+{
+	const unsigned lane = threadIdx.x & 31u;
+	const unsigned tiles_x = (unsigned)(P.width + 7) >> 3, tiles_y = (unsigned)(P.height + 3) >> 2;
+	uint32_t xy = DRT_QUEUE_NO_PIXEL;
+	bool progress = false;
+	for (int it = 0; it < 2 && idle != 0u; it++) {
+		if (q.cursor == 32u) {
+			// the tile index was requested when the previous tile was opened: the atomic's round trip is off the critical path
+			const unsigned t = __shfl_sync(0xffffffffu, q.pending, 0);
+			if (t >= tiles_x * tiles_y) break;
+			if (lane == 0) q.pending = atomicAdd(P.work_queue, 1u);
+			const unsigned ty = t / tiles_x, tx = t - ty * tiles_x;
+			q.org = (tx * 8u) | ((ty * 4u) << 16);
+			q.cursor = 0u;
+		}
+		const unsigned rank = (unsigned)__popc(idle & ((1u << lane) - 1u));
+		const bool mine = ((idle >> lane) & 1u) != 0u && rank < 32u - q.cursor;
+		if (mine) {
+			const unsigned i = q.cursor + rank;
+			const unsigned x = (q.org & 0xffffu) + (i & 7u), y = (q.org >> 16) + (i >> 3);
+			if (x < (unsigned)P.width && y < (unsigned)P.height) xy = x | (y << 16);
+		}
+		const unsigned taken = __ballot_sync(0xffffffffu, mine);
+		idle &= ~taken;
+		q.cursor += (unsigned)__popc(taken);
+		progress = true;
+	}
+	if (xy != DRT_QUEUE_NO_PIXEL) {
+		const uint32_t x = xy & 0xffffu, y = xy >> 16;
+		LanePath S;
+		const float4 a4 = P.accum[(size_t)x + (size_t)y * (size_t)P.width];
+		S.acc = mk3(a4.x, a4.y, a4.z); S.k = 0; S.fn = mk3(0.f, 0.f, 0.f);
+		path_begin_sample<STRICT>(P, x, y, rtl, S);
+		cold_put3(c, CF_LIGHT, S.light); cold_put3(c, CF_THRU, S.throughput); cold_put3(c, CF_FN, S.fn); cold_put3(c, CF_ACC, S.acc);
+		c[CF_SEED * DRT_COLD_THREADS] = S.seed; c[CF_K * DRT_COLD_THREADS] = S.k; c[CF_BOUNCE * DRT_COLD_THREADS] = (uint32_t)S.bounce;
+		c[CF_XY * DRT_COLD_THREADS] = xy;
+		o = S.o; d = S.d;
+		ray_box_setup(o, d, R);
+		trav_begin(L, FLT_MAX);
+		phase = first_phase;
+	}
+	return progress;
+}
+
+template <bool STRICT, bool STATS, int FMT, bool QUEUE>
+__device__ __forceinline__ void render_warp_cold(const RenderParams& P, const PhasedTuning T, uint32_t x0, uint32_t y0, bool valid0,
+	bool rtl, TraceStats* st, uint8_t* lut, uint32_t* cold)
+{
+	WarpQueue q;
+	q.org = 0u; q.cursor = 32u; q.pending = 0xffffffffu;
+	if (QUEUE && (threadIdx.x & 31) == 0 && P.n_samples > 0) q.pending = atomicAdd(P.work_queue, 1u);
+	int refill_min = (QUEUE && P.n_samples > 0) ? (T.refill > 32 ? 32 : (T.refill < 1 ? 1 : T.refill)) : 33;
+	const uint4 lut_part = permute_lut_load();
+	uint32_t* c = cold + threadIdx.x;
+	LaneTrav L;
+	LaneStack K;
+	RayBox R;
+	V3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
+	bool shadow = false;
+	int phase = PH_DONE;
+	const int first_phase = P.scene.num_nodes > 0 ? PH_NODE : PH_SHADE;
+	trav_begin(L, FLT_MAX);
+	R.oct_inv = 0u;
+	R.idnx = R.idny = R.idnz = R.bnx = R.bny = R.bnz = R.idfx = R.idfy = R.idfz = R.bfx = R.bfy = R.bfz = 0.f;
+	{
+		LanePath S;
+		S.acc = mk3(0.f, 0.f, 0.f); S.k = 0; S.fn = mk3(0.f, 0.f, 0.f);
+		S.o = o; S.d = d;
+		S.light = S.throughput = mk3(0.f, 0.f, 0.f);
+		S.seed = 0; S.bounce = 0; S.shadow = false;
+		uint32_t xy = DRT_QUEUE_NO_PIXEL;
+		if (!QUEUE && valid0) {
+			xy = x0 | (y0 << 16);
+			const float4 a4 = P.accum[(size_t)x0 + (size_t)y0 * (size_t)P.width];
+			S.acc = mk3(a4.x, a4.y, a4.z);
+			if (P.n_samples > 0) {
+				path_begin_sample<STRICT>(P, x0, y0, rtl, S);
+				o = S.o; d = S.d;
+				ray_box_setup(o, d, R);
+				phase = first_phase;
+			}
+		}
+		cold_put3(c, CF_LIGHT, S.light); cold_put3(c, CF_THRU, S.throughput); cold_put3(c, CF_FN, S.fn); cold_put3(c, CF_ACC, S.acc);
+		c[CF_SEED * DRT_COLD_THREADS] = S.seed; c[CF_K * DRT_COLD_THREADS] = S.k; c[CF_BOUNCE * DRT_COLD_THREADS] = (uint32_t)S.bounce;
+		c[CF_CLOSEST * DRT_COLD_THREADS] = 0u; c[CF_SHADOW * DRT_COLD_THREADS] = 0u; c[CF_XY * DRT_COLD_THREADS] = xy;
+	}
+	permute_lut_store(lut, lut_part);
+	for (;;) {
+		const unsigned b0 = __ballot_sync(0xffffffffu, (phase & 1) != 0), b1 = __ballot_sync(0xffffffffu, (phase & 2) != 0);
+		if (QUEUE) {
+			// REFILL step: once at least T.refill lanes idle, they take the next pixels of the warp's queue TOGETHER (rank order
+			// = pixel order of the tile), so that neighbouring pixels start their primary rays in the same steps.
+			const unsigned idle = b0 & b1;
+			if (__popc(idle) >= refill_min) {
+				if (queue_refill<STRICT>(P, q, idle, rtl, c, o, d, R, L, phase, first_phase)) continue;
+				refill_min = 33; // the queue has run out: never again
+			}
+		}
+		if ((b0 & b1) == 0xffffffffu) break;
+		const int cN = __popc(~(b0 | b1)), cT = __popc(b0 & ~b1), cS = __popc(b1 & ~b0);
+		const int pick = (cN >= cT && cN >= cS) ? PH_NODE : (cT >= cS ? PH_TRI : PH_SHADE);
+		do {
+			if (phase == pick) {
+				if (pick == PH_NODE) {
+					if (FMT == NODE_FMT_F32) node_step_f32<STATS>(P.scene.nodes_f32, L, K, R, st, lut);
+					else node_step_q8<STATS>(P.scene.nodes, L, K, R, st, lut);
+					phase = trav_advance(L, K);
+				}
+				else if (pick == PH_TRI) {
+					if (tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, o, d, shadow, st)) phase = PH_SHADE;
+					else phase = trav_advance(L, K);
+				}
+				else {
+					LanePath S;
+					PathCounters pc;
+					S.o = o; S.d = d; S.shadow = shadow;
+					S.light = cold_get3(c, CF_LIGHT); S.throughput = cold_get3(c, CF_THRU); S.fn = cold_get3(c, CF_FN); S.acc = cold_get3(c, CF_ACC);
+					S.seed = c[CF_SEED * DRT_COLD_THREADS]; S.k = c[CF_K * DRT_COLD_THREADS]; S.bounce = (int)c[CF_BOUNCE * DRT_COLD_THREADS];
+					pc.closest = c[CF_CLOSEST * DRT_COLD_THREADS]; pc.shadow = c[CF_SHADOW * DRT_COLD_THREADS];
+					const uint32_t xy = c[CF_XY * DRT_COLD_THREADS];
+					const bool more = shade_step<STRICT, STATS>(P, xy & 0xffffu, xy >> 16, rtl, L.hit, S, pc, st);
+					if (QUEUE && !more) {
+						// all samples of the pixel are in (RenderKernel.cu:29-31); the lane idles until the next refill
+						const size_t p = (size_t)(xy & 0xffffu) + (size_t)(xy >> 16) * (size_t)P.width;
+						P.accum[p] = make_float4(S.acc.x, S.acc.y, S.acc.z, 0.f);
+						P.display[p] = make_float4(S.acc.x / P.total_samples, S.acc.y / P.total_samples, S.acc.z / P.total_samples, 1.f);
+					}
+					cold_put3(c, CF_LIGHT, S.light); cold_put3(c, CF_THRU, S.throughput); cold_put3(c, CF_FN, S.fn); cold_put3(c, CF_ACC, S.acc);
+					c[CF_SEED * DRT_COLD_THREADS] = S.seed; c[CF_K * DRT_COLD_THREADS] = S.k; c[CF_BOUNCE * DRT_COLD_THREADS] = (uint32_t)S.bounce;
+					c[CF_CLOSEST * DRT_COLD_THREADS] = pc.closest; c[CF_SHADOW * DRT_COLD_THREADS] = pc.shadow;
+					o = S.o; d = S.d; shadow = S.shadow;
+					if (!more) phase = PH_DONE;
+					else {
+						ray_box_setup(o, d, R);
+						trav_begin(L, FLT_MAX);
+						phase = first_phase;
+					}
+				}
+			}
+		} while (__popc(__ballot_sync(0xffffffffu, phase == pick)) >= T.stick);
+	}
+}
+
 #endif
 
 

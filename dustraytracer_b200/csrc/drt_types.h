@@ -102,6 +102,7 @@ struct RenderParams {
 	drt_f4* accum;          // W*H rgb sums (a unused)
 	drt_f4* display;        // W*H acc/frameidx, a=1
 	Counters* counters;
+	unsigned* work_queue;   // 2 words, zero between launches: next tile, warps that have left (pixel-queue kernel)
 };
 
 struct Hit {

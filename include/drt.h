@@ -152,10 +152,13 @@ void drt_scene_destroy(drt_scene* scene);
 int drt_renderer_create(int device, drt_renderer** out);
 int drt_renderer_set_stream(drt_renderer* r, void* cuda_stream); /* launch on a caller-owned stream (NULL = own stream) */
 int drt_renderer_set_flags(drt_renderer* r, uint32_t flags);
-/* Kernel selection for measurements: variant 4 = per-warp phase voting over NODE/TRI/SHADE steps, 6 blocks/SM (default;
- * expanded fp32 nodes when the scene has them), 2 = the same without the register cap, 3 = compressed nodes, 0 = flat per-thread state machine,
- * 1 = per-sample bounce loop; block_threads = 0 (default 128) or a multiple of 32 up to 256. Results do not
- * depend on either. */
+/* Kernel selection for measurements. Results do not depend on it. variant -1 (the state of a new renderer) = automatic:
+ * variant 4, except that launches of at most 8 samples are timed on variant 4 and on the persistent pixel-queue kernel
+ * (variant 9) and run on the faster one (re-probed every 256 launches). Explicit values: 4 = per-warp phase voting over
+ * NODE/TRI/SHADE steps, 6 blocks/SM (expanded fp32 nodes when the scene has them), 2 = the same without the register cap,
+ * 3 / 7 / 8 = compressed nodes, 0 = flat per-thread state machine, 1 = per-sample bounce loop, 11-14 = variant 4 / 7 with
+ * the SHADE-only lane state in shared memory (8 / 7 / 6 blocks per SM; 14 = compressed nodes), 9 / 10 = their persistent
+ * pixel-queue form (fp32 / compressed nodes). block_threads = 0 (default 128) or a multiple of 32 up to 256. */
 int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads);
 void drt_renderer_destroy(drt_renderer* r);
 int drt_renderer_kernel_launches(const drt_renderer* r); /* kernels launched by this renderer so far */

@@ -92,7 +92,7 @@ def test_primary_hits_bit_exact(drt, name):
     assert np.all(np.abs(sub[same] - g["tuv_stride4"][0][same]) <= 1e-4 * g["tuv_stride4"][0][same])
 
 
-@pytest.mark.parametrize("variant", [4, 2, 3, 0, 1])
+@pytest.mark.parametrize("variant", [4, 2, 3, 0, 1, 9, 10, 11, 14])
 @pytest.mark.parametrize("name", SCENES)
 def test_accumulated_image_bit_exact(drt, name, variant):
     g = np.load(os.path.join(GOLDEN, "scene_%s.npz" % name))
@@ -149,6 +149,56 @@ def test_production_mode_converged_radiance(drt, name, sun, bounces):
     orc.free(oh)
 
 
+@pytest.mark.parametrize("name,size", [("room", (101, 67)), ("animemaid", (37, 5)), ("cornell_box", (8, 4)), ("dense_monkey", (250, 131))])
+def test_pixel_queue_kernel_matches_fixed_pixel_kernel(drt, name, size):
+    """The kernels that keep the SHADE-only lane state in shared memory (variants 11-14) and their persistent pixel-queue
+    form (variants 9 / 10, what one-sample launches run) against the all-register fixed-pixel kernel in production arithmetic: ragged image sizes, 1..3 samples per launch, several launches, same bits and ray counts."""
+    scene = gpu_scene(drt, name)
+    cam = drt.Camera()
+    st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=4, max_samples=100000)
+
+    def run(variant, batches):
+        r = drt.Renderer()
+        r.set_tuning(variant, 0)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(*size)
+        for b in batches:
+            r.Render(cam, scene, b)
+        return r.readback(drt.DRT_ACCUM_RGB32F), r.readback(drt.DRT_RGBA32F), r.counters()
+
+    for batches in ([1, 1, 1, 1, 1], [3, 2], [5]):
+        a4, d4, c4 = run(4, batches)
+        a3, d3, c3 = run(3, batches)
+        for variant in (9, 10, 11, 12, 13, 14):
+            a, d, c = run(variant, batches)
+            ref_a, ref_d, ref_c = (a3, d3, c3) if variant in (10, 14) else (a4, d4, c4)
+            assert np.array_equal(bits(a), bits(ref_a)) and np.array_equal(bits(d), bits(ref_d)), (variant, batches)
+            assert c == ref_c, (variant, batches)
+
+
+def test_launch_autotuner_is_invisible_in_the_results(drt):
+    """A renderer left on automatic kernel selection times the fixed-pixel and the pixel-queue kernels on its first
+    one-sample launches and keeps the faster one: the accumulated image must not depend on what it picked."""
+    scene = gpu_scene(drt, "room")
+    cam = drt.Camera()
+    st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=8, max_samples=100000)
+
+    def run(explicit, calls):
+        r = drt.Renderer()
+        if explicit is not None:
+            r.set_tuning(explicit, 0)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(480, 270)
+        for n in calls:
+            r.Render(cam, scene, n)
+        return r.readback(drt.DRT_ACCUM_RGB32F), r.counters(), r.kernel_launches()
+
+    calls = [1] * 20 + [3, 3, 3, 3, 3, 3, 3, 3] + [16]
+    a, ca, la = run(None, calls)
+    b, cb, lb = run(4, calls)
+    assert np.array_equal(bits(a), bits(b)) and ca == cb and la == lb
+
+
 def test_full_size_properties(drt):
     """BASELINE config-3 size (room, 1920x1080, sun, 8 bounces): determinism, batching invariance, sample-range
     sharding = partition of the frames, ray accounting."""
@@ -181,8 +231,8 @@ def test_full_size_properties(drt):
     assert np.abs((s0 + s1) - a).max() <= 4 * np.finfo(np.float32).eps * np.abs(a).max()
     # strict arithmetic: every kernel variant agrees bit for bit at full size ...
     v4, c4 = run(1, 1, 2, 2, flags=STRICT, variant=4)
-    for variant in (0, 1, 3):
-        v, c = run(1, 1, 2, 2, flags=STRICT, variant=variant)
+    for variant in (0, 1, 3, 9, 10, 11):
+        v, c = run(1, 1, 2, 1 if variant in (9, 10) else 2, flags=STRICT, variant=variant)
         assert np.array_equal(bits(v4), bits(v)) and c["closest_rays"] == c4["closest_rays"], variant
     # ... and with the host-compiled reference (2 of the 256 frames of the 1080p image, a few seconds of CPU)
     orc = O.best_oracle()

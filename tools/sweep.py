@@ -21,12 +21,13 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--scenes", default="room")
     ap.add_argument("--spp", type=int, default=32)
-    ap.add_argument("--variants", default="0,1")
+    ap.add_argument("--variants", default="0,1", help="kernel variants (drt.h); -1 = automatic selection (launch auto-tuner)")
     ap.add_argument("--blocks", default="64,128,256")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--flags", type=int, default=0)
+    ap.add_argument("--calls", type=int, default=1, help="render calls per measurement, --spp samples each (1 = one batched call)")
     ap.add_argument("--bias", default="0:0:0", help="comma list of node:tri:shade vote biases (phased variants)")
     a = ap.parse_args()
     for name in a.scenes.split(","):
@@ -48,15 +49,15 @@ def main():
                 for _ in range(a.reps):
                     r.resetAccumulationBuffer()
                     r.counters(reset=True)
-                    ms = r.Render(cam, scene, a.spp)
+                    ms = sum(r.Render(cam, scene, a.spp) for _ in range(a.calls))
                     c = r.counters()
                     rays = c["closest_rays"] + c["shadow_rays"]
                     if best is None or ms < best[0]:
                         best = (ms, rays, c)
                 ms, rays, c = best
                 out = {"scene": name, "tris": st["triangles"], "wide_nodes": st["wide_nodes"], "build_ms": round(st["build_ms"], 3),
-                       "variant": v, "block": b, "bias": bias, "spp": a.spp, "ms": round(ms, 3), "Mrays_s": round(rays / ms / 1e3, 1),
-                       "Msamples_s": round(a.width * a.height * a.spp / ms / 1e3, 1), "rays": rays}
+                       "variant": v, "block": b, "bias": bias, "spp": a.spp, "calls": a.calls, "ms": round(ms, 3), "ms_per_sample": round(ms / (a.spp * a.calls), 4), "Mrays_s": round(rays / ms / 1e3, 1),
+                       "Msamples_s": round(a.width * a.height * a.spp * a.calls / ms / 1e3, 1), "rays": rays}
                 if a.flags & 4:
                     out.update({"nodes_per_ray": round(c["node_visits"] / rays, 3), "tris_per_ray": round(c["tri_tests"] / rays, 3),
                                 "max_stack": c["max_stack"]})
