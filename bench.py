@@ -256,12 +256,17 @@ def run_ours(args, rank, world, local_rank):
     cam = drt.Camera()
     r = drt.Renderer(device=local_rank)
     r.m_RendererSettings = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=WORKLOAD["bounces"], max_samples=1 << 30)
-    r.set_tuning(int(os.environ.get("DRT_VARIANT", "4")), int(os.environ.get("DRT_BLOCK", "0")))
+    r.set_tuning(int(os.environ.get("DRT_VARIANT", "-1")), int(os.environ.get("DRT_BLOCK", "0")))  # -1 = automatic (variant 4 at this sample count)
     r.ResizeBuffer(W, H)
     stream = torch.cuda.current_stream(dev)
     r.set_stream(stream.cuda_stream)
-    # sample-range sharding: rank g owns frame indices g+1, g+1+world, ...
-    r.set_frame_schedule(rank + 1, world)
+    tiles = args.shard == "tiles"
+    if tiles:
+        # image-tile sharding (strong scaling of one frame): rank g owns the 8x4 tiles g, g+world, ... of every frame
+        r.set_tile_schedule(rank, world)
+    else:
+        # sample-range sharding: rank g owns frame indices g+1, g+1+world, ...
+        r.set_frame_schedule(rank + 1, world)
     ptr, nbytes = r.accum_device_ptr()
     acc_t = torch.as_tensor(_DevPtr(ptr, nbytes // 4), device=dev)
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)  # > 126 MB L2
@@ -275,7 +280,7 @@ def run_ours(args, rank, world, local_rank):
         if world > 1:
             dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
-                r.resolve(SPP * world)
+                r.resolve(SPP if tiles else SPP * world)
         if e2e and rank == 0:
             r.readback(drt.DRT_RGBA32F, out=host_frame_np)
 
@@ -347,7 +352,7 @@ def run_ours(args, rank, world, local_rank):
         ncu = ncu_capture_summary()
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                     "traffic": ncu.get("traffic"), "traffic_note": ncu.get("traffic_note"), "issue": ncu.get("issue"),
-                    "peak_kind": peak_kind, "kernel": "k_render<STRICT=0,STATS=0,VARIANT=%d> (phased, one launch per step)" % int(os.environ.get("DRT_VARIANT", "4")),
+                    "peak_kind": peak_kind, "kernel": "k_render<STRICT=0,STATS=0,VARIANT=%d> (phased, one launch per step)" % max(4, int(os.environ.get("DRT_VARIANT", "4"))),
                     "algorithmic_bytes_per_ray": bytes_per_ray, "node_visits_per_ray": V, "tri_tests_per_ray": T,
                     "note": "scene is cache resident (42 KB): the binding roofline is SM issue rate, see profiles/ and DESIGN.md"}
         # ---- CPU baseline: bounded sample on the host cores ----
@@ -372,11 +377,12 @@ def run_ours(args, rank, world, local_rank):
                 v["Mrays_s_at_our_ray_count"] = rays_per_sample / (v["ms_per_sample"] * 1e-3) / 1e6
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": max_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": max_ms / args.steps, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic camera path over the bundled room scene (fixture re-muxed from the reference model)",
-            "samples_per_s": W * H * SPP * world * args.steps / (max_ms * 1e-3),
-            "config": {"workload": "room.glb 1920x1080, 256 spp per GPU per step, 8 bounces, sun shadow rays (BASELINE config 3)",
-                       **WORKLOAD, "parallelism": "sample-range sharding x%d + NCCL reduce of the accumulation buffer" % world,
+            "samples_per_s": W * H * SPP * (1 if tiles else world) * args.steps / (max_ms * 1e-3),
+            "config": {"workload": "room.glb 1920x1080, %d spp per %s per step, 8 bounces, sun shadow rays (BASELINE config 3)" % (SPP, "frame (all GPUs together)" if tiles else "GPU"),
+                       **WORKLOAD, "parallelism": ("image-tile sharding x%d (8x4 tiles, interleaved) + NCCL reduce of the accumulation buffer" if tiles
+                                                   else "sample-range sharding x%d + NCCL reduce of the accumulation buffer") % world,
                        "l2": "256 MB buffer written between timed steps (L2 flush)", "wide_nodes": sstats["wide_nodes"],
                        "build_ms": sstats["build_ms"]},
             "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 152, "d2h_bytes_per_step": W * H * 16},
@@ -427,19 +433,22 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--shard", default=os.environ.get("DRT_SHARD", "samples"), choices=["samples", "tiles"],
+                    help="N>1: sample-range sharding (weak scaling, default) or image-tile sharding of each frame (strong scaling)")
     args = ap.parse_args()
-    claim_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if not (args.impl != "reference" and world == 1 and args.gpus > 1):
+        claim_stdout()  # (a torchrun re-launch below hands the real stdout to its rank 0 instead)
     if args.impl == "reference":
         return run_reference(args, rank)
     if world == 1 and args.gpus > 1:
         # convenience: re-launch under torchrun
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus), "--master-addr", "127.0.0.1",
                "--master-port", os.environ.get("MASTER_PORT", "29511"), os.path.abspath(__file__), "--gpus", str(args.gpus),
-               "--steps", str(args.steps), "--warmup", str(args.warmup)]
+               "--steps", str(args.steps), "--warmup", str(args.warmup), "--shard", args.shard]
         return subprocess.call(cmd)
     return run_ours(args, rank, world, local_rank)
 

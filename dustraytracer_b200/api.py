@@ -229,6 +229,10 @@ class Renderer:
     def set_frame_schedule(self, first_frame, stride):
         check(_lib.lib().drt_renderer_set_frame_schedule(self._h, first_frame, stride))
 
+    def set_tile_schedule(self, first_tile, stride):
+        """Image-tile sharding: render only the 8x4 tiles first_tile, first_tile+stride, ... (row-major tile index)."""
+        check(_lib.lib().drt_renderer_set_tile_schedule(self._h, first_tile, stride))
+
     def readback(self, fmt=DRT_RGBA32F, out=None):
         w, h = self.getBufferWidth(), self.getBufferHeight()
         shape, dt = {DRT_RGBA32F: ((h, w, 4), np.float32), DRT_RGBA8: ((h, w, 4), np.uint8),
@@ -272,3 +276,13 @@ class Renderer:
                 self._h = ctypes.c_void_p()
         except Exception:
             pass
+
+
+def tile_owner_mask(width, height, first_tile, stride):
+    """Boolean (height, width) mask of the pixels a renderer with set_tile_schedule(first_tile, stride) renders: the 8x4
+    tiles whose row-major index t satisfies t >= first_tile and (t - first_tile) % stride == 0 (drt_kernels.cu pixel_of_thread)."""
+    import numpy as np
+    tiles_x = (width + 7) // 8
+    ys, xs = np.mgrid[0:height, 0:width]
+    t = (ys // 4) * tiles_x + xs // 8
+    return (t >= first_tile) & ((t - first_tile) % stride == 0)

@@ -129,6 +129,7 @@ struct drt_renderer {
 	uint32_t frame_index = 1;   // the reference's m_FrameIndex (Renderer.hpp:41): next frame to render
 	uint32_t samples_done = 0;  // samples accumulated by THIS renderer
 	uint32_t first_frame = 1, stride = 1;
+	uint32_t tile_first = 0, tile_stride = 1; // image-tile sharding (drt_renderer_set_tile_schedule)
 	uint32_t flags = 0;
 	int variant = 4, block_threads = 0;
 	bool auto_variant = true; // no explicit drt_renderer_set_tuning: the launch auto-tuner may pick the kernel
@@ -553,6 +554,14 @@ extern "C" int drt_renderer_set_frame_schedule(drt_renderer* r, uint32_t first_f
 	return drt_renderer_reset(r);
 }
 
+extern "C" int drt_renderer_set_tile_schedule(drt_renderer* r, uint32_t first_tile, uint32_t stride)
+{
+	if (!r || stride == 0 || first_tile >= stride || stride > 65536) return fail(DRT_ERR_INVALID, "drt_renderer_set_tile_schedule: need first_tile < stride <= 65536");
+	r->tile_first = first_tile; r->tile_stride = stride;
+	r->tune = drt_renderer::AutoTune();
+	return drt_renderer_reset(r);
+}
+
 extern "C" int drt_renderer_reset(drt_renderer* r)
 {
 	// resetAccumulationBuffer (Renderer.cu:132-136): zero the sums, frame index back to 1
@@ -601,6 +610,7 @@ static int make_render_params(drt_renderer* r, const drt_camera* cam, const drt_
 	P.width = (int32_t)r->width; P.height = (int32_t)r->height;
 	P.accum = r->accum.p; P.display = r->display.p; P.counters = r->counters.p;
 	P.work_queue = r->work_queue.p;
+	P.tile_first = r->tile_first; P.tile_stride = r->tile_stride;
 	return DRT_OK;
 }
 

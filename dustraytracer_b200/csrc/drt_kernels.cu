@@ -24,12 +24,13 @@ namespace drt {
 
 namespace {
 
-__device__ __forceinline__ void pixel_of_thread(int width, int height, int warps_per_block, int& x, int& y, bool& valid)
+__device__ __forceinline__ void pixel_of_thread(int width, int height, int warps_per_block, uint32_t tile_first, uint32_t tile_stride,
+	int& x, int& y, bool& valid)
 {
-	// 8x4 pixel tile per warp; tiles numbered row-major over the image
+	// 8x4 pixel tile per warp; tiles numbered row-major over the image; a launch owns tiles first, first+stride, ...
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int tiles_x = (width + 7) >> 3;
-	const long long tile = (long long)blockIdx.x * warps_per_block + warp;
+	const long long tile = ((long long)blockIdx.x * warps_per_block + warp) * tile_stride + tile_first;
 	const int ty = (int)(tile / tiles_x), tx = (int)(tile - (long long)ty * tiles_x);
 	x = tx * 8 + (lane & 7);
 	y = ty * 4 + (lane >> 3);
@@ -65,7 +66,7 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 {
 	int x, y;
 	bool valid;
-	pixel_of_thread(P.width, P.height, warps_per_block, x, y, valid);
+	pixel_of_thread(P.width, P.height, warps_per_block, P.tile_first, P.tile_stride, x, y, valid);
 	PathCounters pc;
 	pc.closest = 0; pc.shadow = 0;
 	TraceStats ts;
@@ -122,7 +123,7 @@ __global__ void __launch_bounds__(128, (CV == 1 || CV == 3 || CV == 4) ? 7 : (CV
 	__shared__ uint32_t cold[DRT_COLD_WORDS];
 	int x = 0, y = 0;
 	bool valid = false;
-	if (!QUEUE) pixel_of_thread(P.width, P.height, 4, x, y, valid);
+	if (!QUEUE) pixel_of_thread(P.width, P.height, 4, P.tile_first, P.tile_stride, x, y, valid);
 	render_warp_cold<STRICT, STATS, FMT, QUEUE>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, st, lut, cold);
 	const uint32_t* c = cold + threadIdx.x;
 	if (!QUEUE && valid) {
@@ -150,7 +151,7 @@ __global__ void __launch_bounds__(256) k_trace_primary(const __grid_constant__ R
 {
 	int x, y;
 	bool valid;
-	pixel_of_thread(P.width, P.height, warps_per_block, x, y, valid);
+	pixel_of_thread(P.width, P.height, warps_per_block, 0u, 1u, x, y, valid);
 	TraceStats ts;
 	ts.nodes = ts.tris = ts.ties = ts.alpha = ts.max_stack = ts.clamps = 0;
 	PathCounters pc;
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(256) k_render_ext(const __grid_constant__ Rend
 {
 	int x, y;
 	bool valid;
-	pixel_of_thread(P.width, P.height, warps_per_block, x, y, valid);
+	pixel_of_thread(P.width, P.height, warps_per_block, P.tile_first, P.tile_stride, x, y, valid);
 	PathCounters pc;
 	pc.closest = 0; pc.shadow = 0;
 	TraceStats ts;
@@ -380,7 +381,10 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 {
 	const int threads = cfg.block_threads > 0 ? cfg.block_threads : 128;
 	const int wpb = threads / 32;
-	const long long tiles = (long long)((P.width + 7) / 8) * ((P.height + 3) / 4);
+	const long long all_tiles = (long long)((P.width + 7) / 8) * ((P.height + 3) / 4);
+	if (P.tile_stride == 0) return cudaErrorInvalidValue;
+	const long long tiles = all_tiles > P.tile_first ? (all_tiles - P.tile_first + P.tile_stride - 1) / P.tile_stride : 0; // tiles this launch owns
+	if (tiles == 0) return cudaSuccess;
 	const unsigned blocks = (unsigned)((tiles + wpb - 1) / wpb);
 	PhasedTuning tune;
 	tune.stick = cfg.sched_bias[0] > 0 ? cfg.sched_bias[0] : 6; // measured: room best at 8, dense_monkey at 4 (33 = never)

@@ -627,8 +627,9 @@ __device__ __forceinline__ bool queue_refill(const RenderParams& P, WarpQueue& q
 	for (int it = 0; it < 2 && idle != 0u; it++) {
 		if (q.cursor == 32u) {
 			// the tile index was requested when the previous tile was opened: the atomic's round trip is off the critical path
-			const unsigned t = __shfl_sync(0xffffffffu, q.pending, 0);
-			if (t >= tiles_x * tiles_y) break;
+			const unsigned long long gt = (unsigned long long)__shfl_sync(0xffffffffu, q.pending, 0) * P.tile_stride + P.tile_first; // k-th tile this launch owns
+			if (gt >= (unsigned long long)tiles_x * tiles_y) break;
+			const unsigned t = (unsigned)gt;
 			if (lane == 0) q.pending = atomicAdd(P.work_queue, 1u);
 			const unsigned ty = t / tiles_x, tx = t - ty * tiles_x;
 			q.org = (tx * 8u) | ((ty * 4u) << 16);

@@ -103,6 +103,7 @@ struct RenderParams {
 	drt_f4* display;        // W*H acc/frameidx, a=1
 	Counters* counters;
 	unsigned* work_queue;   // 2 words, zero between launches: next tile, warps that have left (pixel-queue kernel)
+	uint32_t tile_first, tile_stride; // image-tile sharding: this launch owns the 8x4 tiles first, first+stride, ... (row-major tile index)
 };
 
 struct Hit {

@@ -166,6 +166,11 @@ int drt_renderer_kernel_launches(const drt_renderer* r); /* kernels launched by 
 int drt_renderer_upload_accum(drt_renderer* r, const float* rgb32f, size_t bytes, uint32_t samples_done);
 /* Sample-range sharding across GPUs: this renderer renders frame indices first, first+stride, ... (default 1, 1). */
 int drt_renderer_set_frame_schedule(drt_renderer* r, uint32_t first_frame, uint32_t stride);
+/* Image-tile sharding across GPUs (BASELINE config 3): this renderer renders only the 8x4-pixel tiles whose
+ * row-major index is first_tile, first_tile+stride, ... (default 0, 1 = all) and leaves the other pixels of its buffers
+ * untouched (zero after a reset), so that ONE sum-reduce of the accumulation buffers over the ranks yields the bits of
+ * the single-GPU image. Every rank uses the same frame schedule. Resets the accumulation. */
+int drt_renderer_set_tile_schedule(drt_renderer* r, uint32_t first_tile, uint32_t stride);
 int drt_renderer_resize(drt_renderer* r, uint32_t width, uint32_t height);
 /* Renders up to n_samples further samples in one batch (the reference renders one per call) and updates the
  * display buffer; stops at settings->max_samples like Renderer.cu:82. ms = device time of the launch(es). */

@@ -121,6 +121,7 @@ public:
 		return c;
 	}
 	void setFrameSchedule(uint32_t first_frame, uint32_t stride) { check(drt_renderer_set_frame_schedule(h_, first_frame, stride)); }
+	void setTileSchedule(uint32_t first_tile, uint32_t stride) { check(drt_renderer_set_tile_schedule(h_, first_tile, stride)); }
 	drt_renderer* handle() const { return h_; }
 
 private:

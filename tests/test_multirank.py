@@ -69,3 +69,47 @@ def test_two_gloo_ranks_shard_the_frames_and_reduce(tmp_path, world):
         shard, _ = emu.render(h, g["camera"], g["settings"], W, H, rank + 1, world, FRAMES // world, strict=True, rtl=True, steps=1)
         assert np.array_equal(alone.view(np.uint32), shard.view(np.uint32))
     emu.free(h)
+
+
+def _tile_rank_main(rank, world, port, out_path):
+    import torch
+    import torch.distributed as dist
+    import sys
+    sys.path.insert(0, O.ROOT)
+    from dustraytracer_b200.api import tile_owner_mask
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    g = np.load(os.path.join(GOLDEN, "scene_room.npz"))
+    emu = O.HostEmu()
+    h = emu.load(O.scene_path("room"))
+    # drt_renderer_set_tile_schedule(rank, world): every rank renders ALL frames of the tiles it owns; the pixels of the
+    # other ranks stay zero. (The host emulation renders the whole image; the device kernels skip the other tiles.)
+    acc, cnt = emu.render(h, g["camera"], g["settings"], W, H, 1, 1, FRAMES, strict=True, rtl=True, steps=1)
+    own = tile_owner_mask(W, H, rank, world)
+    acc = np.where(np.repeat(own.reshape(-1), 3), acc, np.float32(0))
+    t = torch.from_numpy(acc.copy())
+    pixels = torch.tensor([float(own.sum())], dtype=torch.float64)
+    dist.reduce(t, dst=0, op=dist.ReduceOp.SUM)          # the one collective of the path
+    dist.all_reduce(pixels, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        np.savez(out_path, acc=t.numpy(), pixels=pixels.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+    emu.free(h)
+
+
+@pytest.mark.parametrize("world", [2])
+def test_two_gloo_ranks_shard_the_tiles_and_reduce(tmp_path, world):
+    """Image-tile sharding: the tiles of the ranks partition the image and the reduced sums are the single-rank BITS."""
+    import torch.multiprocessing as mp
+    out_path = str(tmp_path / "rank0.npz")
+    mp.start_processes(_tile_rank_main, args=(world, _free_port(), out_path), nprocs=world, join=True, start_method="spawn")
+    got = np.load(out_path)
+    g = np.load(os.path.join(GOLDEN, "scene_room.npz"))
+    emu = O.HostEmu()
+    h = emu.load(O.scene_path("room"))
+    full, _ = emu.render(h, g["camera"], g["settings"], W, H, 1, 1, FRAMES, strict=True, rtl=True, steps=1)
+    emu.free(h)
+    assert int(got["pixels"][0]) == W * H
+    assert np.array_equal(got["acc"].view(np.uint32), full.view(np.uint32))
