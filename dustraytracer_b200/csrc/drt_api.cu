@@ -144,10 +144,13 @@ struct drt_renderer {
 		const void* scene = nullptr;
 		uint32_t w = 0, h = 0, n = 0, flags = 0;
 		int32_t bounce = -1, sun = -1;
-		int step = 0;                          // < 2 * candidates: probing candidate step % candidates
+		int step = 0;                          // < passes * candidates: probing candidate step % candidates
 		float best_ms[3] = { 0.f, 0.f, 0.f };
 		int choice = 0;
 		int settled_launches = 0;
+		int period = 256;                      // launches between probe rounds; doubles (up to 4096) while the choice stands
+		int passes = 2;                        // timings per candidate in a round: 2 for a new key (the first launch of a kernel
+		                                       // in a process pays its load), 1 afterwards
 	} tune;
 	int sm_count = 0;
 	int kernel_launches = 0;
@@ -616,6 +619,7 @@ static int make_render_params(drt_renderer* r, const drt_camera* cam, const drt_
 
 #define DRT_AUTOTUNE_CANDIDATES 3
 #define DRT_AUTOTUNE_PERIOD 256
+#define DRT_AUTOTUNE_PERIOD_MAX 4096
 
 // Candidate c of the launch auto-tuner: 0 = fixed-pixel kernel, 1 / 2 = pixel-queue kernel with an early / late refill.
 static void autotune_apply(int c, uint32_t n, LaunchConfig& cfg)
@@ -623,6 +627,18 @@ static void autotune_apply(int c, uint32_t n, LaunchConfig& cfg)
 	if (c == 0) return;
 	cfg.variant = 9;
 	cfg.sched_bias[1] = c == 1 ? 4 : (n <= 1 ? 16 : 10);
+}
+
+// End of a probe round: keep the fastest candidate; the interval to the next round doubles while the choice stands.
+static void autotune_settle(drt_renderer::AutoTune& t)
+{
+	int choice = 0;
+	for (int c = 1; c < DRT_AUTOTUNE_CANDIDATES; c++)
+		if (t.best_ms[c] < 0.98f * t.best_ms[choice]) choice = c; // the fixed-pixel kernel keeps ties
+	t.period = (choice == t.choice && t.period > 0) ? (2 * t.period > DRT_AUTOTUNE_PERIOD_MAX ? DRT_AUTOTUNE_PERIOD_MAX : 2 * t.period) : DRT_AUTOTUNE_PERIOD;
+	t.choice = choice;
+	t.settled_launches = 0;
+	t.passes = 1; // later rounds find the kernels loaded and warm: one timing per candidate
 }
 
 // Returns the candidate this launch runs (and whether its time is a probe), or -1 when the launch is not eligible.
@@ -635,10 +651,11 @@ static int autotune_pick(drt_renderer* r, const drt_scene* scene, const RenderPa
 	if (t.scene != scene || t.w != (uint32_t)P.width || t.h != (uint32_t)P.height || t.n != P.n_samples || t.flags != r->flags ||
 		t.bounce != P.shade.bounce_limit || t.sun != P.shade.enable_sunlight) {
 		t = drt_renderer::AutoTune();
+		t.period = 0; // (first round of this key: the period starts at DRT_AUTOTUNE_PERIOD)
 		t.scene = scene; t.w = (uint32_t)P.width; t.h = (uint32_t)P.height; t.n = P.n_samples; t.flags = r->flags;
 		t.bounce = P.shade.bounce_limit; t.sun = P.shade.enable_sunlight;
 	}
-	if (t.step < 2 * DRT_AUTOTUNE_CANDIDATES) { probing = true; return t.step % DRT_AUTOTUNE_CANDIDATES; }
+	if (t.step < t.passes * DRT_AUTOTUNE_CANDIDATES) { probing = true; return t.step % DRT_AUTOTUNE_CANDIDATES; }
 	return t.choice;
 }
 
@@ -646,15 +663,11 @@ static void autotune_record(drt_renderer* r, int candidate, bool probing, float 
 {
 	drt_renderer::AutoTune& t = r->tune;
 	if (!probing) {
-		if (++t.settled_launches >= DRT_AUTOTUNE_PERIOD) { t.step = 0; t.settled_launches = 0; }
+		if (++t.settled_launches >= t.period) t.step = 0; // next probe round
 		return;
 	}
 	if (t.step < DRT_AUTOTUNE_CANDIDATES || ms < t.best_ms[candidate]) t.best_ms[candidate] = ms;
-	if (++t.step == 2 * DRT_AUTOTUNE_CANDIDATES) {
-		t.choice = 0;
-		for (int c = 1; c < DRT_AUTOTUNE_CANDIDATES; c++)
-			if (t.best_ms[c] < 0.98f * t.best_ms[t.choice]) t.choice = c; // the fixed-pixel kernel keeps ties
-	}
+	if (++t.step == t.passes * DRT_AUTOTUNE_CANDIDATES) autotune_settle(t);
 }
 
 static LaunchConfig launch_config(const drt_renderer* r)

@@ -154,7 +154,7 @@ int drt_renderer_set_stream(drt_renderer* r, void* cuda_stream); /* launch on a 
 int drt_renderer_set_flags(drt_renderer* r, uint32_t flags);
 /* Kernel selection for measurements. Results do not depend on it. variant -1 (the state of a new renderer) = automatic:
  * variant 4, except that launches of at most 8 samples are timed on variant 4 and on the persistent pixel-queue kernel
- * (variant 9) and run on the faster one (re-probed every 256 launches). Explicit values: 4 = per-warp phase voting over
+ * (variant 9) and run on the faster one (re-probed after 256, 512, ... 4096 launches). Explicit values: 4 = per-warp phase voting over
  * NODE/TRI/SHADE steps, 6 blocks/SM (expanded fp32 nodes when the scene has them), 2 = the same without the register cap,
  * 3 / 7 / 8 = compressed nodes, 0 = flat per-thread state machine, 1 = per-sample bounce loop, 11-14 = variant 4 / 7 with
  * the SHADE-only lane state in shared memory (8 / 7 / 6 blocks per SM; 14 = compressed nodes), 9 / 10 = their persistent

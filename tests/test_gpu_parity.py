@@ -234,6 +234,30 @@ def test_tile_sharding_is_a_partition_of_the_image(drt, variant):
         assert rays == cfull["closest_rays"] + cfull["shadow_rays"]
 
 
+def test_empty_scene_renders_the_sky_in_every_kernel(drt):
+    """Zero triangles (the edge the reference never guards: its builder dereferences an empty vector): every ray misses, every
+    sample is one closest-hit ray and the sky; all kernel families agree bit for bit, ragged size included."""
+    scene = drt.Scene.from_triangles(np.zeros((0, 3, 3), np.float32))
+    drt.BVHBuilder().buildIterative(scene)
+    cam = drt.Camera()
+    st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=3, max_samples=1000)
+    W, H, spp = 61, 35, 3
+    ref = None
+    for variant in (4, 0, 1, 3, 9, 10, 11):
+        r = drt.Renderer(flags=STRICT)
+        r.set_tuning(variant, 0)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(W, H)
+        r.Render(cam, scene, spp)
+        r.Render(cam, scene)
+        a, c = r.readback(drt.DRT_ACCUM_RGB32F), r.counters()
+        assert c["closest_rays"] == W * H * (spp + 1) and c["shadow_rays"] == 0
+        assert np.isfinite(a).all() and a.min() > 0
+        if ref is None:
+            ref = a
+        assert np.array_equal(bits(a), bits(ref)), variant
+
+
 def test_full_size_properties(drt):
     """BASELINE config-3 size (room, 1920x1080, sun, 8 bounces): determinism, batching invariance, sample-range
     sharding = partition of the frames, ray accounting."""

@@ -127,7 +127,8 @@ def main():
         if a.variant >= 0 or a.block:
             r.set_tuning(a.variant if a.variant >= 0 else 4, a.block)
         r.ResizeBuffer(W, H)
-        r.Render(cam, scene, min(spp, 2))  # warm-up
+        for _ in range(8 if spp <= 8 else 1):  # warm-up (few-sample launches: also lets the launch auto-tuner settle)
+            r.Render(cam, scene, min(spp, 2))
         r.resetAccumulationBuffer()
         r.counters(reset=True)
         ms = r.Render(cam, scene, spp)
