@@ -15,7 +15,13 @@
 //                              4 is the default: issue-slot utilisation rises with occupancy up to 6 blocks (profiles/)
 //   variant 7, 8 phased, Q8    variant 3 compiled for 8 / 6 blocks per SM; 7 is what scenes without expanded nodes get
 //                              (soup-10M is latency-bound: +17 % from the extra resident warps)
-// Warps cover 8x4 pixel tiles (coherent primary rays); blocks are rows of such tiles.
+//   variant 11..14 cold state   variant 4 / 7 with the SHADE-only lane state in shared memory (k_render_cold: 11 / 12 / 13 = fp32 nodes at
+//                              8 / 7 / 6 blocks per SM, 14 = compressed nodes); measured alternatives
+//   variant 9, 10 pixel queue  persistent form of the cold-state kernel for launches of FEW samples (the reference renders one per
+//                              launch): warps pull 8x4 tiles from a global counter, idle lanes take new pixels together (REFILL step);
+//                              chosen against variant 4 by the renderer's launch auto-tuner (drt_api.cu)
+// Warps cover 8x4 pixel tiles (coherent primary rays); blocks are rows of such tiles. A launch may own only the tiles
+// first, first+stride, ... (image-tile sharding across GPUs, RenderParams::tile_first / tile_stride).
 #include "drt_kernels.h"
 #include "drt_shade.cuh"
 #include "drt_phased.cuh"
