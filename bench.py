@@ -260,13 +260,21 @@ def run_ours(args, rank, world, local_rank):
     r.ResizeBuffer(W, H)
     stream = torch.cuda.current_stream(dev)
     r.set_stream(stream.cuda_stream)
-    tiles = args.shard == "tiles"
+    p2p = args.shard == "p2p"
+    tiles = args.shard in ("tiles", "p2p")
     if tiles:
         # image-tile sharding (strong scaling of one frame): rank g owns the 8x4 tiles g, g+world, ... of every frame
         r.set_tile_schedule(rank, world)
     else:
         # sample-range sharding: rank g owns frame indices g+1, g+1+world, ...
         r.set_frame_schedule(rank + 1, world)
+    if p2p and world > 1:
+        # image tiles WITHOUT a collective: every rank's kernel stores its tiles straight into rank 0's frame buffers
+        # (CUDA IPC mapping + peer access over NVLink); the only cross-rank traffic besides those stores is the barrier
+        box = [r.export_frame_buffers() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        if rank != 0:
+            r.import_frame_buffers(box[0])
     ptr, nbytes = r.accum_device_ptr()
     acc_t = torch.as_tensor(_DevPtr(ptr, nbytes // 4), device=dev)
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)  # > 126 MB L2
@@ -275,9 +283,13 @@ def run_ours(args, rank, world, local_rank):
 
     def step(e2e):
         """reset -> one batched 256-spp launch -> (N>1: NCCL reduce) -> (rank 0: resolve) [-> host readback]"""
-        r.resetAccumulationBuffer()
+        r.resetAccumulationBuffer()          # (p2p: rank 0 zeroes the shared buffers, the others only their sample counters)
+        if p2p and world > 1:
+            dist.barrier()                   # nobody stores into the shared buffers before they are zeroed
         r.Render(cam, scene, SPP)
-        if world > 1:
+        if p2p and world > 1:
+            dist.barrier()                   # the frame (sums and display) is complete in rank 0's buffers
+        elif world > 1:
             dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
                 r.resolve(SPP if tiles else SPP * world)
@@ -381,7 +393,8 @@ def run_ours(args, rank, world, local_rank):
             "data": "synthetic camera path over the bundled room scene (fixture re-muxed from the reference model)",
             "samples_per_s": W * H * SPP * (1 if tiles else world) * args.steps / (max_ms * 1e-3),
             "config": {"workload": "room.glb 1920x1080, %d spp per %s per step, 8 bounces, sun shadow rays (BASELINE config 3)" % (SPP, "frame (all GPUs together)" if tiles else "GPU"),
-                       **WORKLOAD, "parallelism": ("image-tile sharding x%d (8x4 tiles, interleaved) + NCCL reduce of the accumulation buffer" if tiles
+                       **WORKLOAD, "parallelism": ("image-tile sharding x%d (8x4 tiles, interleaved), peer stores into rank 0's frame buffers over NVLink, no collective" if p2p
+                                                   else "image-tile sharding x%d (8x4 tiles, interleaved) + NCCL reduce of the accumulation buffer" if tiles
                                                    else "sample-range sharding x%d + NCCL reduce of the accumulation buffer") % world,
                        "l2": "256 MB buffer written between timed steps (L2 flush)", "wide_nodes": sstats["wide_nodes"],
                        "build_ms": sstats["build_ms"]},
@@ -433,8 +446,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--shard", default=os.environ.get("DRT_SHARD", "samples"), choices=["samples", "tiles"],
-                    help="N>1: sample-range sharding (weak scaling, default) or image-tile sharding of each frame (strong scaling)")
+    ap.add_argument("--shard", default=os.environ.get("DRT_SHARD", "samples"), choices=["samples", "tiles", "p2p"],
+                    help="N>1: sample-range sharding (weak scaling, default), image-tile sharding of each frame + reduce (strong scaling), "
+                         "or image tiles stored directly into rank 0's buffers over NVLink (p2p)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

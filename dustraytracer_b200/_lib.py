@@ -87,6 +87,9 @@ SIGNATURES = {
     "drt_renderer_set_tuning": (_i, [_vp, ctypes.c_int32, ctypes.c_int32]),
     "drt_renderer_set_frame_schedule": (_i, [_vp, _u, _u]),
     "drt_renderer_set_tile_schedule": (_i, [_vp, _u, _u]),
+    "drt_renderer_export_frame_buffers": (_i, [_vp, _vp]),
+    "drt_renderer_import_frame_buffers": (_i, [_vp, _vp]),
+    "drt_renderer_attach_frame_buffers": (_i, [_vp, _vp]),
     "drt_renderer_resize": (_i, [_vp, _u, _u]),
     "drt_renderer_render": (_i, [_vp, _P(drt_camera), _vp, _P(drt_settings), _u, _P(ctypes.c_float)]),
     "drt_renderer_reset": (_i, [_vp]),

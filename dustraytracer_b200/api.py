@@ -182,6 +182,9 @@ class BVHBuilder:
     buildIterative = build
 
 
+DRT_FRAME_HANDLE_BYTES = 160
+
+
 class Renderer:
     """class Renderer (Core/Renderer.hpp:14-47), headless: a device float4 frame buffer replaces the GL texture."""
 
@@ -228,6 +231,21 @@ class Renderer:
 
     def set_frame_schedule(self, first_frame, stride):
         check(_lib.lib().drt_renderer_set_frame_schedule(self._h, first_frame, stride))
+
+    def export_frame_buffers(self):
+        """Bytes another process hands to import_frame_buffers to render its tiles directly into THIS renderer's buffers."""
+        buf = ctypes.create_string_buffer(DRT_FRAME_HANDLE_BYTES)
+        check(_lib.lib().drt_renderer_export_frame_buffers(self._h, buf))
+        return bytes(buf.raw)
+
+    def import_frame_buffers(self, handle):
+        buf = ctypes.create_string_buffer(bytes(handle), DRT_FRAME_HANDLE_BYTES)
+        check(_lib.lib().drt_renderer_import_frame_buffers(self._h, buf))
+
+    def attach_frame_buffers(self, owner):
+        """Same process: render into `owner`'s buffers (None detaches)."""
+        check(_lib.lib().drt_renderer_attach_frame_buffers(self._h, owner._h if owner is not None else None))
+        self._fb_owner = owner  # keep the buffers alive
 
     def set_tile_schedule(self, first_tile, stride):
         """Image-tile sharding: render only the 8x4 tiles first_tile, first_tile+stride, ... (row-major tile index)."""

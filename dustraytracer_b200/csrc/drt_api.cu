@@ -122,6 +122,12 @@ struct drt_renderer {
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	uint32_t width = 0, height = 0;
 	DevBuf<drt_f4> accum, display;
+	// frame buffers of ANOTHER renderer this one renders into (image-tile sharding without a collective): set by
+	// drt_renderer_attach_frame_buffers (same process) or drt_renderer_import_frame_buffers (CUDA IPC, another process)
+	drt_f4* ext_accum = nullptr;
+	drt_f4* ext_display = nullptr;
+	void* ipc_accum = nullptr;   // mappings to close
+	void* ipc_display = nullptr;
 	DevBuf<Counters> counters;
 	DevBuf<unsigned> work_queue; // pixel-queue kernel: next tile, warps that have left (the kernel leaves both at zero)
 	DevBuf<Hit> hits;
@@ -482,6 +488,17 @@ extern "C" int drt_scene_get_leaf_triangles(const drt_scene* scene, void* out, s
 // ---------------------------------------------------------------------------------------------
 // renderer
 // ---------------------------------------------------------------------------------------------
+static drt_f4* fb_accum(const drt_renderer* r) { return r->ext_accum ? r->ext_accum : r->accum.p; }
+static drt_f4* fb_display(const drt_renderer* r) { return r->ext_display ? r->ext_display : r->display.p; }
+
+static void detach_frame_buffers(drt_renderer* r)
+{
+	if (r->ipc_accum) cudaIpcCloseMemHandle(r->ipc_accum);
+	if (r->ipc_display) cudaIpcCloseMemHandle(r->ipc_display);
+	r->ipc_accum = r->ipc_display = nullptr;
+	r->ext_accum = r->ext_display = nullptr;
+}
+
 static int renderer_bind(drt_renderer* r)
 {
 	DRT_CUDA(cudaSetDevice(r->device));
@@ -519,6 +536,7 @@ extern "C" void drt_renderer_destroy(drt_renderer* r)
 	if (!r) return;
 	cudaSetDevice(r->device);
 	cudaStreamSynchronize(r->stream);
+	detach_frame_buffers(r);
 	if (r->ev0) cudaEventDestroy(r->ev0);
 	if (r->ev1) cudaEventDestroy(r->ev1);
 	if (r->own_stream) cudaStreamDestroy(r->own_stream);
@@ -565,13 +583,81 @@ extern "C" int drt_renderer_set_tile_schedule(drt_renderer* r, uint32_t first_ti
 	return drt_renderer_reset(r);
 }
 
+// ---- frame-buffer sharing: image-tile sharding where every rank's kernel stores its tiles straight into the root's buffers ----
+struct FrameHandle {
+	cudaIpcMemHandle_t accum, display;
+	uint32_t width, height;
+	int32_t device;
+	uint32_t magic;
+};
+static_assert(sizeof(FrameHandle) <= DRT_FRAME_HANDLE_BYTES, "frame handle must fit the ABI's byte array");
+#define DRT_FRAME_MAGIC 0x44525446u
+
+extern "C" int drt_renderer_export_frame_buffers(drt_renderer* r, void* handle_out)
+{
+	if (!r || !handle_out || !r->width) return fail(DRT_ERR_INVALID, "drt_renderer_export_frame_buffers: renderer has no buffer");
+	if (r->ext_accum) return fail(DRT_ERR_INVALID, "drt_renderer_export_frame_buffers: this renderer renders into another renderer's buffers");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	FrameHandle h;
+	memset(&h, 0, sizeof(h));
+	DRT_CUDA(cudaIpcGetMemHandle(&h.accum, r->accum.p));
+	DRT_CUDA(cudaIpcGetMemHandle(&h.display, r->display.p));
+	h.width = r->width; h.height = r->height; h.device = r->device; h.magic = DRT_FRAME_MAGIC;
+	memset(handle_out, 0, DRT_FRAME_HANDLE_BYTES);
+	memcpy(handle_out, &h, sizeof(h));
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_import_frame_buffers(drt_renderer* r, const void* handle)
+{
+	if (!r || !handle || !r->width) return fail(DRT_ERR_INVALID, "drt_renderer_import_frame_buffers: resize the renderer first");
+	FrameHandle h;
+	memcpy(&h, handle, sizeof(h));
+	if (h.magic != DRT_FRAME_MAGIC) return fail(DRT_ERR_INVALID, "drt_renderer_import_frame_buffers: not a frame-buffer handle");
+	if (h.width != r->width || h.height != r->height) return fail(DRT_ERR_INVALID, "drt_renderer_import_frame_buffers: size differs from the exporting renderer");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	detach_frame_buffers(r);
+	void* a = nullptr;
+	void* d = nullptr;
+	// (maps the exporter's allocation into this process and enables peer access to its device: loads and stores go over NVLink)
+	DRT_CUDA(cudaIpcOpenMemHandle(&a, h.accum, cudaIpcMemLazyEnablePeerAccess));
+	cudaError_t e = cudaIpcOpenMemHandle(&d, h.display, cudaIpcMemLazyEnablePeerAccess);
+	if (e != cudaSuccess) { cudaIpcCloseMemHandle(a); return fail(DRT_ERR_CUDA, std::string("drt_renderer_import_frame_buffers: ") + cudaGetErrorString(e)); }
+	r->ipc_accum = a; r->ipc_display = d;
+	r->ext_accum = (drt_f4*)a; r->ext_display = (drt_f4*)d;
+	return drt_renderer_reset(r);
+}
+
+extern "C" int drt_renderer_attach_frame_buffers(drt_renderer* r, drt_renderer* owner)
+{
+	if (!r || !r->width) return fail(DRT_ERR_INVALID, "drt_renderer_attach_frame_buffers: resize the renderer first");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	detach_frame_buffers(r);
+	if (!owner || owner == r) return drt_renderer_reset(r);
+	if (owner->ext_accum) return fail(DRT_ERR_INVALID, "drt_renderer_attach_frame_buffers: the owner renders into another renderer's buffers itself");
+	if (owner->width != r->width || owner->height != r->height) return fail(DRT_ERR_INVALID, "drt_renderer_attach_frame_buffers: size differs from the owner");
+	if (owner->device != r->device) {
+		int can = 0;
+		DRT_CUDA(cudaDeviceCanAccessPeer(&can, r->device, owner->device));
+		if (!can) return fail(DRT_ERR_CUDA, "drt_renderer_attach_frame_buffers: no peer access between the two devices");
+		cudaError_t e = cudaDeviceEnablePeerAccess(owner->device, 0);
+		if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+		else if (e != cudaSuccess) return fail(DRT_ERR_CUDA, std::string("drt_renderer_attach_frame_buffers: ") + cudaGetErrorString(e));
+	}
+	r->ext_accum = owner->accum.p; r->ext_display = owner->display.p;
+	return drt_renderer_reset(r);
+}
+
 extern "C" int drt_renderer_reset(drt_renderer* r)
 {
 	// resetAccumulationBuffer (Renderer.cu:132-136): zero the sums, frame index back to 1
 	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_reset: null renderer");
 	if (renderer_bind(r)) return DRT_ERR_CUDA;
-	if (r->accum.n) DRT_CUDA(cudaMemsetAsync(r->accum.p, 0, r->accum.bytes(), r->stream));
-	if (r->display.n) DRT_CUDA(cudaMemsetAsync(r->display.p, 0, r->display.bytes(), r->stream));
+	// (a renderer attached to another renderer's frame buffers leaves zeroing them to their owner)
+	if (r->accum.n && !r->ext_accum) DRT_CUDA(cudaMemsetAsync(r->accum.p, 0, r->accum.bytes(), r->stream));
+	if (r->display.n && !r->ext_display) DRT_CUDA(cudaMemsetAsync(r->display.p, 0, r->display.bytes(), r->stream));
 	r->frame_index = 1;
 	r->samples_done = 0;
 	return DRT_OK;
@@ -585,6 +671,7 @@ extern "C" int drt_renderer_resize(drt_renderer* r, uint32_t width, uint32_t hei
 	if (width == r->width && height == r->height) return DRT_OK;
 	if (renderer_bind(r)) return DRT_ERR_CUDA;
 	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	detach_frame_buffers(r); // shared buffers have the old size
 	const size_t n = (size_t)width * height;
 	DRT_CUDA(r->accum.alloc(n));
 	DRT_CUDA(r->display.alloc(n));
@@ -611,7 +698,7 @@ static int make_render_params(drt_renderer* r, const drt_camera* cam, const drt_
 	if (!settings) { default_settings(&dflt); settings = &dflt; }
 	P.shade = make_shade_params(*settings);
 	P.width = (int32_t)r->width; P.height = (int32_t)r->height;
-	P.accum = r->accum.p; P.display = r->display.p; P.counters = r->counters.p;
+	P.accum = fb_accum(r); P.display = fb_display(r); P.counters = r->counters.p;
 	P.work_queue = r->work_queue.p;
 	P.tile_first = r->tile_first; P.tile_stride = r->tile_stride;
 	return DRT_OK;
@@ -730,7 +817,7 @@ extern "C" int drt_renderer_resolve(drt_renderer* r, uint32_t total_samples)
 {
 	if (!r || !r->width || total_samples == 0) return fail(DRT_ERR_INVALID, "drt_renderer_resolve: bad argument");
 	if (renderer_bind(r)) return DRT_ERR_CUDA;
-	DRT_CUDA(launch_resolve(r->display.p, r->accum.p, (int)((size_t)r->width * r->height), (float)total_samples, r->stream));
+	DRT_CUDA(launch_resolve(fb_display(r), fb_accum(r), (int)((size_t)r->width * r->height), (float)total_samples, r->stream));
 	r->kernel_launches++;
 	DRT_CUDA(cudaStreamSynchronize(r->stream));
 	return DRT_OK;
@@ -739,7 +826,7 @@ extern "C" int drt_renderer_resolve(drt_renderer* r, uint32_t total_samples)
 extern "C" int drt_renderer_accum_device_ptr(drt_renderer* r, void** ptr, size_t* bytes)
 {
 	if (!r || !ptr || !r->width) return fail(DRT_ERR_INVALID, "drt_renderer_accum_device_ptr: renderer has no buffer");
-	*ptr = r->accum.p;
+	*ptr = fb_accum(r);
 	if (bytes) *bytes = r->accum.bytes();
 	return DRT_OK;
 }
@@ -751,14 +838,14 @@ extern "C" int drt_renderer_readback(drt_renderer* r, drt_format format, void* h
 	const size_t n = (size_t)r->width * r->height;
 	if (format == DRT_RGBA32F) {
 		if (bytes < n * 16) return fail(DRT_ERR_INVALID, "drt_renderer_readback: buffer too small");
-		DRT_CUDA(cudaMemcpyAsync(host, r->display.p, n * 16, cudaMemcpyDeviceToHost, r->stream));
+		DRT_CUDA(cudaMemcpyAsync(host, fb_display(r), n * 16, cudaMemcpyDeviceToHost, r->stream));
 	}
 	else if (format == DRT_RGBA8 || format == DRT_ACCUM_RGB32F) {
 		const size_t need = format == DRT_RGBA8 ? n * 4 : n * 12;
 		if (bytes < need) return fail(DRT_ERR_INVALID, "drt_renderer_readback: buffer too small");
 		if (r->staging.n < need) DRT_CUDA(r->staging.alloc(need));
-		if (format == DRT_RGBA8) DRT_CUDA(launch_pack_rgba8((uint32_t*)r->staging.p, r->display.p, (int)n, r->stream));
-		else DRT_CUDA(launch_pack_rgb32f((float*)r->staging.p, r->accum.p, (int)n, r->stream));
+		if (format == DRT_RGBA8) DRT_CUDA(launch_pack_rgba8((uint32_t*)r->staging.p, fb_display(r), (int)n, r->stream));
+		else DRT_CUDA(launch_pack_rgb32f((float*)r->staging.p, fb_accum(r), (int)n, r->stream));
 		r->kernel_launches++;
 		DRT_CUDA(cudaMemcpyAsync(host, r->staging.p, need, cudaMemcpyDeviceToHost, r->stream));
 	}
@@ -776,7 +863,7 @@ extern "C" int drt_renderer_upload_accum(drt_renderer* r, const float* rgb32f, s
 	if (bytes < n * 12) return fail(DRT_ERR_INVALID, "drt_renderer_upload_accum: buffer too small");
 	std::vector<drt_f4> tmp(n);
 	for (size_t i = 0; i < n; i++) { tmp[i].x = rgb32f[3 * i]; tmp[i].y = rgb32f[3 * i + 1]; tmp[i].z = rgb32f[3 * i + 2]; tmp[i].w = 0.f; }
-	DRT_CUDA(cudaMemcpyAsync(r->accum.p, tmp.data(), n * 16, cudaMemcpyHostToDevice, r->stream));
+	DRT_CUDA(cudaMemcpyAsync(fb_accum(r), tmp.data(), n * 16, cudaMemcpyHostToDevice, r->stream));
 	DRT_CUDA(cudaStreamSynchronize(r->stream));
 	r->samples_done = samples_done;
 	r->frame_index = samples_done + 1;

@@ -171,6 +171,18 @@ int drt_renderer_set_frame_schedule(drt_renderer* r, uint32_t first_frame, uint3
  * untouched (zero after a reset), so that ONE sum-reduce of the accumulation buffers over the ranks yields the bits of
  * the single-GPU image. Every rank uses the same frame schedule. Resets the accumulation. */
 int drt_renderer_set_tile_schedule(drt_renderer* r, uint32_t first_tile, uint32_t stride);
+/* Image-tile sharding WITHOUT a collective: the renderers of the other ranks render their tiles directly into the root
+ * renderer's accumulation and display buffers (peer stores over NVLink / NVSwitch from inside the render kernel), so a frame
+ * is complete on the root as soon as every rank's launch has returned -- no reduce, no zeroing of foreign pixels, no resolve.
+ *   export: the root (an ordinary, resized renderer) writes DRT_FRAME_HANDLE_BYTES bytes to send to the other PROCESSES;
+ *   import: a renderer of the same size in another process (any device of the node) maps them (CUDA IPC + peer access);
+ *   attach: the same for two renderers of ONE process (owner == NULL detaches).
+ * An attached / importing renderer keeps its own frame schedule, tile schedule and counters; its reset leaves the shared
+ * buffers to their owner. The caller orders the ranks (barrier after the owner's reset and after the launches). */
+#define DRT_FRAME_HANDLE_BYTES 160
+int drt_renderer_export_frame_buffers(drt_renderer* r, void* handle_out);
+int drt_renderer_import_frame_buffers(drt_renderer* r, const void* handle);
+int drt_renderer_attach_frame_buffers(drt_renderer* r, drt_renderer* owner);
 int drt_renderer_resize(drt_renderer* r, uint32_t width, uint32_t height);
 /* Renders up to n_samples further samples in one batch (the reference renders one per call) and updates the
  * display buffer; stops at settings->max_samples like Renderer.cu:82. ms = device time of the launch(es). */

@@ -258,6 +258,90 @@ def test_empty_scene_renders_the_sky_in_every_kernel(drt):
         assert np.array_equal(bits(a), bits(ref)), variant
 
 
+def _ipc_child(handle, W, H, first, stride, batches, q):
+    """Another PROCESS (spawned): imports the parent's frame buffers and renders its tiles into them."""
+    try:
+        import dustraytracer_b200 as d
+        scene = d.Scene()
+        scene.loadGLTFmodel(O.scene_path("room"))
+        d.BVHBuilder().buildIterative(scene)
+        r = d.Renderer(flags=STRICT)
+        r.m_RendererSettings = d.RendererSettings(enable_sunlight=1, ray_bounce_limit=4, max_samples=100000)
+        r.ResizeBuffer(W, H)
+        r.set_tile_schedule(first, stride)
+        r.import_frame_buffers(handle)
+        for b in batches:
+            r.Render(d.Camera(), scene, b)
+        c = r.counters()
+        q.put(("ok", c["closest_rays"] + c["shadow_rays"]))
+    except Exception as e:  # noqa: BLE001
+        q.put(("error", repr(e)))
+
+
+def test_tiles_rendered_straight_into_a_shared_frame_buffer(drt):
+    """Image-tile sharding without a collective: renderers that own the other tiles store them directly into the root
+    renderer's buffers -- attached in the same process, and imported over CUDA IPC by another process. The root then
+    holds the bits of the unsharded render, display included, with nothing to reduce or resolve."""
+    import multiprocessing as mp
+    scene = gpu_scene(drt, "room")
+    W, H = 203, 117
+    cam = drt.Camera()
+    st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=4, max_samples=100000)
+    batches = [1, 2, 1]
+
+    def make(first, stride):
+        r = drt.Renderer(flags=STRICT)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(W, H)
+        r.set_tile_schedule(first, stride)
+        return r
+
+    full = make(0, 1)
+    for b in batches:
+        full.Render(cam, scene, b)
+    ref_a, ref_d, ref_c = full.readback(drt.DRT_ACCUM_RGB32F), full.readback(drt.DRT_RGBA32F), full.counters()
+
+    # same process: rank 0 owns the buffers, "ranks" 1 and 2 are attached to them
+    root = make(0, 3)
+    peers = [make(1, 3), make(2, 3)]
+    for p in peers:
+        p.attach_frame_buffers(root)
+    rays = 0
+    for b in batches:
+        for r in [root] + peers:
+            r.Render(cam, scene, b)
+    for r in [root] + peers:
+        c = r.counters()
+        rays += c["closest_rays"] + c["shadow_rays"]
+    assert np.array_equal(bits(root.readback(drt.DRT_ACCUM_RGB32F)), bits(ref_a))
+    assert np.array_equal(bits(root.readback(drt.DRT_RGBA32F)), bits(ref_d))
+    assert np.array_equal(bits(peers[0].readback(drt.DRT_ACCUM_RGB32F)), bits(ref_a)), "an attached renderer reads the shared buffer"
+    assert rays == ref_c["closest_rays"] + ref_c["shadow_rays"]
+    peers[0].resetAccumulationBuffer()
+    assert np.array_equal(bits(root.readback(drt.DRT_ACCUM_RGB32F)), bits(ref_a)), "a peer's reset leaves the owner's buffers alone"
+    peers[1].attach_frame_buffers(None)
+    assert not peers[1].readback(drt.DRT_ACCUM_RGB32F).any(), "detached: back on its own (zeroed) buffers"
+
+    # another process: CUDA IPC
+    root2 = make(0, 2)
+    handle = root2.export_frame_buffers()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    child = ctx.Process(target=_ipc_child, args=(handle, W, H, 1, 2, batches, q))
+    child.start()
+    for b in batches:
+        root2.Render(cam, scene, b)
+    status, val = q.get(timeout=300)
+    child.join(60)
+    assert status == "ok", val
+    c = root2.counters()
+    assert val + c["closest_rays"] + c["shadow_rays"] == ref_c["closest_rays"] + ref_c["shadow_rays"]
+    assert np.array_equal(bits(root2.readback(drt.DRT_ACCUM_RGB32F)), bits(ref_a))
+    assert np.array_equal(bits(root2.readback(drt.DRT_RGBA32F)), bits(ref_d))
+    with pytest.raises(drt.DrtError):
+        make(0, 1).import_frame_buffers(b"\0" * 160)
+
+
 def test_full_size_properties(drt):
     """BASELINE config-3 size (room, 1920x1080, sun, 8 bounces): determinism, batching invariance, sample-range
     sharding = partition of the frames, ray accounting."""
