@@ -275,6 +275,9 @@ def run_ours(args, rank, world, local_rank):
         dist.broadcast_object_list(box, src=0)
         if rank != 0:
             r.import_frame_buffers(box[0])
+        from dustraytracer_b200.node_barrier import NodeBarrier
+        node_barrier = NodeBarrier("drt-bench-%s" % os.environ.get("MASTER_PORT", "0"), rank, world)
+        dist.barrier()
     ptr, nbytes = r.accum_device_ptr()
     acc_t = torch.as_tensor(_DevPtr(ptr, nbytes // 4), device=dev)
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)  # > 126 MB L2
@@ -285,10 +288,12 @@ def run_ours(args, rank, world, local_rank):
         """reset -> one batched 256-spp launch -> (N>1: NCCL reduce) -> (rank 0: resolve) [-> host readback]"""
         r.resetAccumulationBuffer()          # (p2p: rank 0 zeroes the shared buffers, the others only their sample counters)
         if p2p and world > 1:
-            dist.barrier()                   # nobody stores into the shared buffers before they are zeroed
-        r.Render(cam, scene, SPP)
+            if rank == 0:
+                stream.synchronize()         # the shared buffers are zeroed ...
+            node_barrier.wait()              # ... before anybody stores into them (host barrier in shared memory, a few us)
+        r.Render(cam, scene, SPP)            # (returns with this rank's tiles stored)
         if p2p and world > 1:
-            dist.barrier()                   # the frame (sums and display) is complete in rank 0's buffers
+            node_barrier.wait()              # the frame (sums and display) is complete in rank 0's buffers
         elif world > 1:
             dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
@@ -393,7 +398,7 @@ def run_ours(args, rank, world, local_rank):
             "data": "synthetic camera path over the bundled room scene (fixture re-muxed from the reference model)",
             "samples_per_s": W * H * SPP * (1 if tiles else world) * args.steps / (max_ms * 1e-3),
             "config": {"workload": "room.glb 1920x1080, %d spp per %s per step, 8 bounces, sun shadow rays (BASELINE config 3)" % (SPP, "frame (all GPUs together)" if tiles else "GPU"),
-                       **WORKLOAD, "parallelism": ("image-tile sharding x%d (8x4 tiles, interleaved), peer stores into rank 0's frame buffers over NVLink, no collective" if p2p
+                       **WORKLOAD, "parallelism": ("image-tile sharding x%d (8x4 tiles, interleaved), peer stores into rank 0's frame buffers over NVLink, no collective (host barrier in shared memory)" if p2p
                                                    else "image-tile sharding x%d (8x4 tiles, interleaved) + NCCL reduce of the accumulation buffer" if tiles
                                                    else "sample-range sharding x%d + NCCL reduce of the accumulation buffer") % world,
                        "l2": "256 MB buffer written between timed steps (L2 flush)", "wide_nodes": sstats["wide_nodes"],
@@ -406,6 +411,8 @@ def run_ours(args, rank, world, local_rank):
         emit_json_line(line)
     if world > 1:
         dist.barrier()
+        if p2p:
+            node_barrier.close()
         dist.destroy_process_group()
     return 0
 

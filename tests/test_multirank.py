@@ -113,3 +113,28 @@ def test_two_gloo_ranks_shard_the_tiles_and_reduce(tmp_path, world):
     emu.free(h)
     assert int(got["pixels"][0]) == W * H
     assert np.array_equal(got["acc"].view(np.uint32), full.view(np.uint32))
+
+
+def _barrier_rank(rank, world, name, rounds, out_dir):
+    import sys
+    sys.path.insert(0, O.ROOT)
+    from dustraytracer_b200.node_barrier import NodeBarrier
+    b = NodeBarrier(name, rank, world)
+    log = []
+    for k in range(rounds):
+        # a rank may only see round k of the others once they have all entered round k
+        with open(os.path.join(out_dir, "r%d" % rank), "w") as f:
+            f.write(str(k))
+        b.wait()
+        seen = [int(open(os.path.join(out_dir, "r%d" % r)).read() or -1) for r in range(world)]
+        log.append(min(seen) >= k)
+        b.wait()
+    b.close()
+    assert all(log), log
+
+
+def test_node_barrier_orders_three_processes(tmp_path):
+    """The shared-memory barrier the shared-frame-buffer mode uses instead of a collective."""
+    import torch.multiprocessing as mp
+    world = 3
+    mp.start_processes(_barrier_rank, args=(world, "drt-test-%d" % os.getpid(), 200, str(tmp_path)), nprocs=world, join=True, start_method="spawn")
