@@ -562,7 +562,7 @@ extern "C" int drt_renderer_set_flags(drt_renderer* r, uint32_t flags)
 extern "C" int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads)
 {
 	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: null renderer");
-	if (variant < -1 || variant > 14 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
+	if (variant < -1 || variant > 15 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
 	r->auto_variant = variant < 0;
 	r->variant = variant < 0 ? 4 : variant; r->block_threads = block_threads;
 	return DRT_OK;
@@ -765,6 +765,7 @@ static LaunchConfig launch_config(const drt_renderer* r)
 	cfg.stats = (r->flags & DRT_FLAG_STATS) != 0;
 	cfg.ext_materials = (r->flags & DRT_FLAG_EXTENDED_MATERIALS) != 0;
 	cfg.variant = r->variant; cfg.block_threads = r->block_threads;
+	cfg.auto_variant = r->auto_variant;
 	cfg.resident_sms = r->sm_count;
 	for (int i = 0; i < 3; i++) cfg.sched_bias[i] = r->sched_bias[i];
 	return cfg;

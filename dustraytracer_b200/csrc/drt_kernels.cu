@@ -15,6 +15,8 @@
 //                              4 is the default: issue-slot utilisation rises with occupancy up to 6 blocks (profiles/)
 //   variant 7, 8 phased, Q8    variant 3 compiled for 8 / 6 blocks per SM; 7 is what scenes without expanded nodes get
 //                              (soup-10M is latency-bound: +17 % from the extra resident warps)
+//   variant 15 phased, TRI2   variant 4 whose TRI step tests up to two pending triangles (independent instruction streams, half the voted
+//                              steps for lanes with two or more pending): what automatic selection runs on scenes of >= 1024 triangles
 //   variant 11..14 cold state   variant 4 / 7 with the SHADE-only lane state in shared memory (k_render_cold: 11 / 12 / 13 = fp32 nodes at
 //                              8 / 7 / 6 blocks per SM, 14 = compressed nodes); measured alternatives
 //   variant 9, 10 pixel queue  persistent form of the cold-state kernel for launches of FEW samples (the reference renders one per
@@ -67,7 +69,7 @@ __device__ __forceinline__ void flush_counters(Counters* c, const PathCounters& 
 }
 
 template <bool STRICT, bool STATS, int VARIANT>
-__global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (VARIANT == 8 ? 6 : (VARIANT >= 4 ? VARIANT + 2 : 1))) k_render(const __grid_constant__ RenderParams P, const bool rtl, const int warps_per_block,
+__global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : ((VARIANT == 8 || VARIANT == 15) ? 6 : (VARIANT >= 4 ? VARIANT + 2 : 1))) k_render(const __grid_constant__ RenderParams P, const bool rtl, const int warps_per_block,
 	const PhasedTuning tune)
 {
 	int x, y;
@@ -84,7 +86,7 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 		V3 acc = mk3(0.f, 0.f, 0.f);
 		if (valid) { const float4 a4 = P.accum[p]; acc = mk3(a4.x, a4.y, a4.z); }
 		__shared__ alignas(16) uint8_t lut[DRT_PERMUTE_LUT_BYTES];
-		acc = render_warp_phased<STRICT, STATS, (VARIANT == 3 || VARIANT >= 7) ? NODE_FMT_Q8 : NODE_FMT_F32>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st, lut);
+		acc = render_warp_phased<STRICT, STATS, (VARIANT == 3 || VARIANT == 7 || VARIANT == 8) ? NODE_FMT_Q8 : NODE_FMT_F32, VARIANT == 15>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st, lut);
 		if (valid) {
 			P.accum[p] = make_float4(acc.x, acc.y, acc.z, 0.f);
 			P.display[p] = make_float4(acc.x / P.total_samples, acc.y / P.total_samples, acc.z / P.total_samples, 1.f);
@@ -433,11 +435,14 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 			return cudaGetLastError();
 		}
 	}
+	if (cfg.auto_variant && variant == 4 && P.scene.num_tris >= DRT_TRI2_MIN_TRIS) variant = 15;
+	if (variant == 15 && (P.scene.nodes_f32 == nullptr || threads > 128)) variant = 4; // (two-triangle TRI step: fp32 nodes, 128 threads)
 	if ((variant == 2 || (variant >= 4 && variant <= 6)) && P.scene.nodes_f32 == nullptr) variant = threads <= 128 ? 7 : 3;
 	if (variant >= 7 && threads > 128) variant = 3;
 	if (variant >= 4 && variant <= 6 && threads > 128) variant = 2;
 	if (variant == 7) k_render<STRICT, STATS, 7><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else if (variant == 8) k_render<STRICT, STATS, 8><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+	else if (variant == 15) k_render<STRICT, STATS, 15><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else
 	if (variant == 4) k_render<STRICT, STATS, 4><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else if (variant == 5) k_render<STRICT, STATS, 5><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);

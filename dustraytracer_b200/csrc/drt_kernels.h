@@ -11,12 +11,19 @@ namespace drt {
 #define DRT_QUEUE_MAX_SPP_DEFAULT 8
 #endif
 
+// Automatic kernel selection: from this many triangles on, the two-triangle TRI step (variant 15) replaces variant 4
+// (measured: +4 % to +10 % on the 6 k - 16 k triangle scenes, -1 % on the 34- and 330-triangle ones).
+#ifndef DRT_TRI2_MIN_TRIS
+#define DRT_TRI2_MIN_TRIS 1024
+#endif
+
 struct LaunchConfig {
 	bool strict = false;  // DRT_FLAG_STRICT
 	bool rtl = false;     // DRT_FLAG_HOST_ARG_ORDER
 	bool stats = false;   // DRT_FLAG_STATS
 	bool ext_materials = false; // DRT_FLAG_EXTENDED_MATERIALS: emissive / metal / dielectric shading (reference-shaped loop kernel)
 	int variant = 4;      // render kernel variant (see drt_kernels.cu); 4 = default
+	bool auto_variant = false; // variant 4 was not asked for explicitly: scenes of DRT_TRI2_MIN_TRIS triangles or more run variant 15
 	int sched_bias[3] = { 0, 0, 0 }; // phased kernels: [0] = sticky re-issue threshold (0 = default 6, 33 = never)
 	int block_threads = 0; // 0 = variant default
 	int resident_sms = 0;  // SM count of the device (grid of the persistent kernel)

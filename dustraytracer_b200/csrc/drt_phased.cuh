@@ -344,6 +344,80 @@ DRT_HD bool tri_step(const SceneView& sc, const drt_f4* tris, LaneTrav& L, V3 o,
 	return false;
 }
 
+// Geometric part of one Moller-Trumbore test, computed unconditionally (Intersection.cu:8-33, the reference's operation
+// order; a rejected triangle may produce inf / NaN in t, u, v, which nobody reads).
+struct TriGeo {
+	float t, u, v;
+	bool ok;
+};
+template <bool STRICT>
+DRT_HD TriGeo tri_geometry(const drt_f4 r0, const drt_f4 r1, const drt_f4 r2, V3 o, V3 d)
+{
+	typedef M<STRICT> m;
+	const V3 v0 = mk3(r0.x, r0.y, r0.z), e1 = mk3(r1.x, r1.y, r1.z), e2 = mk3(r2.x, r2.y, r2.z);
+	const V3 pvec = m::cross(d, e2);
+	const float det = m::dot(e1, pvec);
+	const float inv_det = m::div(1.0f, det);
+	const V3 tvec = m::sub3(o, v0);
+	TriGeo g;
+	g.u = m::mul(inv_det, m::dot(tvec, pvec));
+	const V3 qvec = m::cross(tvec, e1);
+	g.v = m::mul(inv_det, m::dot(d, qvec));
+	g.t = m::mul(inv_det, m::dot(e2, qvec));
+	g.ok = !(det > -DRT_TRIANGLE_EPSILON && det < DRT_TRIANGLE_EPSILON) && !(g.u < 0.0f || g.u > 1.0f) && !(g.v < 0.0f || m::add(g.u, g.v) > 1.0f) &&
+		(g.t > DRT_TRIANGLE_EPSILON);
+	return g;
+}
+
+// Closest / any-hit bookkeeping of one geometrically accepted candidate (the tail of tri_step). Returns true when an any-hit
+// ray is finished.
+template <bool STRICT>
+DRT_HD bool tri_apply(const SceneView& sc, const drt_f4* tris, LaneTrav& L, int slot, const drt_f4 r0, const drt_f4 r1, const TriGeo g,
+	bool anyhit, TraceStats* st)
+{
+	if (!g.ok) return false;
+	const uint32_t matw = as_uint(r1.w);
+	if (anyhit) {
+		if ((matw & 0x80000000u) && !alpha_accept<STRICT>(sc, slot, matw & 0x7fffffffu, g.u, g.v, st)) return false;
+		L.hit.prim = slot; L.hit.t = g.t;
+		return true;
+	}
+	if (!(g.t < L.hit.t)) {
+		if (!(g.t == L.hit.t) || L.hit.prim < 0) return false;
+		if (st) st->ties++;
+		const uint32_t id = as_uint(r0.w), best_id = as_uint(ld_f4(tris + 3 * (size_t)L.hit.prim).w);
+		if (!(id < best_id)) return false;
+	}
+	if ((matw & 0x80000000u) && !alpha_accept<STRICT>(sc, slot, matw & 0x7fffffffu, g.u, g.v, st)) return false;
+	L.hit.prim = slot; L.hit.t = g.t;
+	return false;
+}
+
+// TRI step on up to TWO pending triangles: their tests are independent instruction streams (the step is bound by dependent
+// fixed-latency chains), and a lane with two or more pending triangles needs half the voted steps. The candidates are
+// applied in the order tri_step would have met them, the second only if the first did not finish an any-hit ray.
+template <bool STRICT, bool STATS>
+DRT_HD bool tri_step2(const SceneView& sc, const drt_f4* tris, LaneTrav& L, V3 o, V3 d, bool anyhit, TraceStats* st)
+{
+	const int k0 = lo_bit(L.tri_bits);
+	L.tri_bits &= L.tri_bits - 1u;
+	const bool two = L.tri_bits != 0u;
+	const int k1 = two ? lo_bit(L.tri_bits) : k0;
+	const int slot0 = (int)(L.tri_base + (uint32_t)k0), slot1 = (int)(L.tri_base + (uint32_t)k1);
+	const drt_f4* tp0 = tris + 3 * (size_t)slot0;
+	const drt_f4* tp1 = tris + 3 * (size_t)slot1;
+	const drt_f4 a0 = ld_f4(tp0), a1 = ld_f4(tp0 + 1), a2 = ld_f4(tp0 + 2);
+	const drt_f4 b0 = ld_f4(tp1), b1 = ld_f4(tp1 + 1), b2 = ld_f4(tp1 + 2);
+	const TriGeo ga = tri_geometry<STRICT>(a0, a1, a2, o, d);
+	const TriGeo gb = tri_geometry<STRICT>(b0, b1, b2, o, d);
+	if (STATS && st) st->tris++;
+	if (tri_apply<STRICT>(sc, tris, L, slot0, a0, a1, ga, anyhit, st)) return true;
+	if (!two) return false;
+	L.tri_bits &= L.tri_bits - 1u;
+	if (STATS && st) st->tris++;
+	return tri_apply<STRICT>(sc, tris, L, slot1, b0, b1, gb, anyhit, st);
+}
+
 // Barycentrics of the accepted hit, recomputed with the operations of tri_step (Intersection.cu:8-27) when a
 // textured material needs them: cheaper than carrying u, v through every step of every lane.
 template <bool STRICT>
@@ -525,7 +599,7 @@ __device__ __forceinline__ void permute_lut_store(uint8_t* lut, uint4 v)
 }
 
 // One warp: every lane owns one pixel (valid or not) for all samples of the launch.
-template <bool STRICT, bool STATS, int FMT>
+template <bool STRICT, bool STATS, int FMT, bool TRI2 = false>
 __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const PhasedTuning T, uint32_t x, uint32_t y, bool valid,
 	bool rtl, V3 acc, PathCounters& pc, TraceStats* st, uint8_t* lut)
 {
@@ -566,7 +640,8 @@ __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const Ph
 					phase = trav_advance(L, K);
 				}
 				else if (pick == PH_TRI) {
-					if (tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)) phase = PH_SHADE;
+					if (TRI2 ? tri_step2<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)
+					         : tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)) phase = PH_SHADE;
 					else phase = trav_advance(L, K);
 				}
 				else {

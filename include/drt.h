@@ -153,7 +153,8 @@ int drt_renderer_create(int device, drt_renderer** out);
 int drt_renderer_set_stream(drt_renderer* r, void* cuda_stream); /* launch on a caller-owned stream (NULL = own stream) */
 int drt_renderer_set_flags(drt_renderer* r, uint32_t flags);
 /* Kernel selection for measurements. Results do not depend on it. variant -1 (the state of a new renderer) = automatic:
- * variant 4, except that launches of at most 8 samples are timed on variant 4 and on the persistent pixel-queue kernel
+ * variant 4 (scenes of 1024 triangles or more: variant 15 = variant 4 with a TRI step that tests two pending triangles at once),
+ * except that launches of at most 8 samples are timed on variant 4 and on the persistent pixel-queue kernel
  * (variant 9) and run on the faster one (re-probed after 256, 512, ... 4096 launches). Explicit values: 4 = per-warp phase voting over
  * NODE/TRI/SHADE steps, 6 blocks/SM (expanded fp32 nodes when the scene has them), 2 = the same without the register cap,
  * 3 / 7 / 8 = compressed nodes, 0 = flat per-thread state machine, 1 = per-sample bounce loop, 11-14 = variant 4 / 7 with

@@ -92,7 +92,7 @@ def test_primary_hits_bit_exact(drt, name):
     assert np.all(np.abs(sub[same] - g["tuv_stride4"][0][same]) <= 1e-4 * g["tuv_stride4"][0][same])
 
 
-@pytest.mark.parametrize("variant", [4, 2, 3, 0, 1, 9, 10, 11, 14])
+@pytest.mark.parametrize("variant", [4, 2, 3, 0, 1, 9, 10, 11, 14, 15])
 @pytest.mark.parametrize("name", SCENES)
 def test_accumulated_image_bit_exact(drt, name, variant):
     g = np.load(os.path.join(GOLDEN, "scene_%s.npz" % name))
@@ -169,7 +169,7 @@ def test_pixel_queue_kernel_matches_fixed_pixel_kernel(drt, name, size):
     for batches in ([1, 1, 1, 1, 1], [3, 2], [5]):
         a4, d4, c4 = run(4, batches)
         a3, d3, c3 = run(3, batches)
-        for variant in (9, 10, 11, 12, 13, 14):
+        for variant in (9, 10, 11, 12, 13, 14, 15):
             a, d, c = run(variant, batches)
             ref_a, ref_d, ref_c = (a3, d3, c3) if variant in (10, 14) else (a4, d4, c4)
             assert np.array_equal(bits(a), bits(ref_a)) and np.array_equal(bits(d), bits(ref_d)), (variant, batches)
@@ -374,7 +374,7 @@ def test_full_size_properties(drt):
     assert np.abs((s0 + s1) - a).max() <= 4 * np.finfo(np.float32).eps * np.abs(a).max()
     # strict arithmetic: every kernel variant agrees bit for bit at full size ...
     v4, c4 = run(1, 1, 2, 2, flags=STRICT, variant=4)
-    for variant in (0, 1, 3, 9, 10, 11):
+    for variant in (0, 1, 3, 9, 10, 11, 15):
         v, c = run(1, 1, 2, 1 if variant in (9, 10) else 2, flags=STRICT, variant=variant)
         assert np.array_equal(bits(v4), bits(v)) and c["closest_rays"] == c4["closest_rays"], variant
     # ... and with the host-compiled reference (2 of the 256 frames of the 1080p image, a few seconds of CPU)
