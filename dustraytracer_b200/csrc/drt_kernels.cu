@@ -116,13 +116,14 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 // Phased kernel with the SHADE-only lane state in shared memory (drt_phased.cuh render_warp_cold).
 //   CV 0 / 1 / 2 : fixed pixel per lane, expanded fp32 nodes, 8 / 7 / 6 resident blocks per SM   (variants 11 / 12 / 13)
 //   CV 5         : fixed pixel per lane, compressed nodes, 8 blocks per SM                        (variant 14)
-//   CV 3 / 4     : persistent pixel-queue kernel, fp32 / compressed nodes, 8 blocks per SM        (variants 9 / 10):
+//   CV 3 / 4 / 6 : persistent pixel-queue kernel, fp32 / compressed nodes / fp32 + two-triangle TRI step, 7 blocks per SM (variants 9 / 10):
 //                  grid = resident blocks of the device, warps pull 8x4 tiles from P.work_queue[0]; the last warp to
 //                  leave resets the queue words for the next launch.
 template <bool STRICT, bool STATS, int CV>
-__global__ void __launch_bounds__(128, (CV == 1 || CV == 3 || CV == 4) ? 7 : (CV == 2 ? 6 : 8)) k_render_cold(const __grid_constant__ RenderParams P, const bool rtl, const PhasedTuning tune)
+__global__ void __launch_bounds__(128, (CV == 1 || CV == 3 || CV == 4 || CV == 6) ? 7 : (CV == 2 ? 6 : 8)) k_render_cold(const __grid_constant__ RenderParams P, const bool rtl, const PhasedTuning tune)
 {
-	constexpr bool QUEUE = CV == 3 || CV == 4;
+	constexpr bool QUEUE = CV == 3 || CV == 4 || CV == 6;
+	constexpr bool TRI2 = CV == 6; // two-triangle TRI step (scenes of DRT_TRI2_MIN_TRIS triangles or more)
 	constexpr int FMT = (CV == 4 || CV == 5) ? NODE_FMT_Q8 : NODE_FMT_F32;
 	TraceStats ts;
 	ts.nodes = ts.tris = ts.ties = ts.alpha = ts.max_stack = ts.clamps = 0;
@@ -132,7 +133,7 @@ __global__ void __launch_bounds__(128, (CV == 1 || CV == 3 || CV == 4) ? 7 : (CV
 	int x = 0, y = 0;
 	bool valid = false;
 	if (!QUEUE) pixel_of_thread(P.width, P.height, 4, P.tile_first, P.tile_stride, x, y, valid);
-	render_warp_cold<STRICT, STATS, FMT, QUEUE>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, st, lut, cold);
+	render_warp_cold<STRICT, STATS, FMT, QUEUE, TRI2>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, st, lut, cold);
 	const uint32_t* c = cold + threadIdx.x;
 	if (!QUEUE && valid) {
 		const size_t p = (size_t)x + (size_t)y * (size_t)P.width;
@@ -413,6 +414,7 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 		if (!ok) variant = q8 ? 7 : 4;
 		else if (queue) {
 			// persistent grid = what is resident at once (asked from the runtime: a block that had to wait would find the queue empty)
+			const bool tri2 = !q8 && cfg.auto_variant && P.scene.num_tris >= DRT_TRI2_MIN_TRIS;
 			static int per_sm[2] = { 0, 0 };
 			if (per_sm[q8 ? 1 : 0] == 0) {
 				int nb = 0;
@@ -424,6 +426,7 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 			long long qblocks = (long long)cfg.resident_sms * per_sm[q8 ? 1 : 0];
 			if (qblocks * wpb > tiles) qblocks = (tiles + wpb - 1) / wpb; // at least one tile per warp
 			if (q8) k_render_cold<STRICT, STATS, 4><<<(unsigned)qblocks, threads, 0, s>>>(P, cfg.rtl, tune);
+			else if (tri2) k_render_cold<STRICT, STATS, 6><<<(unsigned)qblocks, threads, 0, s>>>(P, cfg.rtl, tune);
 			else k_render_cold<STRICT, STATS, 3><<<(unsigned)qblocks, threads, 0, s>>>(P, cfg.rtl, tune);
 			return cudaGetLastError();
 		}

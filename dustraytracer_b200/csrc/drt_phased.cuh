@@ -739,7 +739,7 @@ __device__ __forceinline__ bool queue_refill(const RenderParams& P, WarpQueue& q
 	return progress;
 }
 
-template <bool STRICT, bool STATS, int FMT, bool QUEUE>
+template <bool STRICT, bool STATS, int FMT, bool QUEUE, bool TRI2 = false>
 __device__ __forceinline__ void render_warp_cold(const RenderParams& P, const PhasedTuning T, uint32_t x0, uint32_t y0, bool valid0,
 	bool rtl, TraceStats* st, uint8_t* lut, uint32_t* cold)
 {
@@ -804,7 +804,8 @@ __device__ __forceinline__ void render_warp_cold(const RenderParams& P, const Ph
 					phase = trav_advance(L, K);
 				}
 				else if (pick == PH_TRI) {
-					if (tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, o, d, shadow, st)) phase = PH_SHADE;
+					if (TRI2 ? tri_step2<STRICT, STATS>(P.scene, P.scene.tris, L, o, d, shadow, st)
+					         : tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, o, d, shadow, st)) phase = PH_SHADE;
 					else phase = trav_advance(L, K);
 				}
 				else {

@@ -176,10 +176,12 @@ def test_pixel_queue_kernel_matches_fixed_pixel_kernel(drt, name, size):
             assert c == ref_c, (variant, batches)
 
 
-def test_launch_autotuner_is_invisible_in_the_results(drt):
+@pytest.mark.parametrize("name", ["room", "animemaid"])
+def test_launch_autotuner_is_invisible_in_the_results(drt, name):
     """A renderer left on automatic kernel selection times the fixed-pixel and the pixel-queue kernels on its first
-    one-sample launches and keeps the faster one: the accumulated image must not depend on what it picked."""
-    scene = gpu_scene(drt, "room")
+    one-sample launches and keeps the faster one: the accumulated image must not depend on what it picked. (animemaid has more
+    than 1024 triangles: automatic selection then also runs the two-triangle TRI step, in both kernel families.)"""
+    scene = gpu_scene(drt, name)
     cam = drt.Camera()
     st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=8, max_samples=100000)
 
