@@ -525,7 +525,7 @@ DRT_HD bool shade_step(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, 
 }
 
 // One lane, serial schedule: the CPU logic tests (tests/hostemu) drive the very same steps with it.
-template <bool STRICT, bool STATS, int FMT>
+template <bool STRICT, bool STATS, int FMT, bool TRI2 = false>
 DRT_HD V3 render_pixel_steps(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, V3 acc, PathCounters& pc, TraceStats* st)
 {
 	if (P.n_samples == 0) return acc;
@@ -545,7 +545,8 @@ DRT_HD V3 render_pixel_steps(const RenderParams& P, uint32_t x, uint32_t y, bool
 			phase = trav_advance(L, K);
 		}
 		else if (phase == PH_TRI) {
-			if (tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)) phase = PH_SHADE;
+			if (TRI2 ? tri_step2<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)
+			         : tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)) phase = PH_SHADE;
 			else phase = trav_advance(L, K);
 		}
 		else {

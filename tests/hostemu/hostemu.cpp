@@ -373,7 +373,9 @@ void emu_render_steps(void* h, const drt_camera* cam, const drt_settings* st, in
 			float* a = acc + 3 * ((size_t)x + (size_t)y * W);
 			V3 in = mk3(a[0], a[1], a[2]), r;
 			const bool rt = rtl != 0;
-			if (strict) r = fmt ? render_pixel_steps<true, true, NODE_FMT_F32>(P, x, y, rt, in, pc, &ts) : render_pixel_steps<true, true, NODE_FMT_Q8>(P, x, y, rt, in, pc, &ts);
+			// fmt: 0 = compressed nodes, 1 = expanded nodes, 2 = expanded nodes + the two-triangle TRI step (tri_step2)
+			if (fmt == 2) r = strict ? render_pixel_steps<true, true, NODE_FMT_F32, true>(P, x, y, rt, in, pc, &ts) : render_pixel_steps<false, true, NODE_FMT_F32, true>(P, x, y, rt, in, pc, &ts);
+			else if (strict) r = fmt ? render_pixel_steps<true, true, NODE_FMT_F32>(P, x, y, rt, in, pc, &ts) : render_pixel_steps<true, true, NODE_FMT_Q8>(P, x, y, rt, in, pc, &ts);
 			else r = fmt ? render_pixel_steps<false, true, NODE_FMT_F32>(P, x, y, rt, in, pc, &ts) : render_pixel_steps<false, true, NODE_FMT_Q8>(P, x, y, rt, in, pc, &ts);
 			a[0] = r.x; a[1] = r.y; a[2] = r.z;
 		}

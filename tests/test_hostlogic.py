@@ -122,10 +122,15 @@ def test_scene_logic_against_golden(emu, name):
         assert np.array_equal(bits(acc), bits(g["acc"])), "flat=%s" % flat
         assert cnt[0] == int(g["rays"][0]) and cnt[1] == int(g["rays"][1])
     # the phased kernel's NODE / TRI / SHADE steps (serial schedule), on both node formats
-    for fmt in (0, 1):
+    # (fmt 2 = expanded nodes with the two-triangle TRI step: same bits, same rays, and the same NUMBER of triangle tests,
+    # because the second candidate is only applied -- and counted -- when the first did not finish an any-hit ray)
+    tests_seen = {}
+    for fmt in (0, 1, 2):
         acc, cnt = emu.render(h, g["camera"], g["settings"], rw, rh, 1, 1, frames, strict=True, rtl=True, steps=fmt)
         assert np.array_equal(bits(acc), bits(g["acc"])), "steps fmt=%d" % fmt
         assert cnt[0] == int(g["rays"][0]) and cnt[1] == int(g["rays"][1])
+        tests_seen[fmt] = (cnt[2], cnt[3])
+    assert tests_seen[2] == tests_seen[1]
     # the five-step decomposition, triangles-first and nodes-first (postponed triangle groups)
     for fmt, nodes_first in ((0, 0), (1, 1), (0, 1)):
         acc, cnt = emu.render(h, g["camera"], g["settings"], rw, rh, 1, 1, frames, strict=True, rtl=True, steps5=(fmt, nodes_first))
