@@ -122,6 +122,11 @@ public:
 	}
 	void setFrameSchedule(uint32_t first_frame, uint32_t stride) { check(drt_renderer_set_frame_schedule(h_, first_frame, stride)); }
 	void setTileSchedule(uint32_t first_tile, uint32_t stride) { check(drt_renderer_set_tile_schedule(h_, first_tile, stride)); }
+	// image-tile sharding without a collective: other renderers store their tiles into THIS renderer's buffers (drt.h)
+	void exportFrameBuffers(void* handle_out /* DRT_FRAME_HANDLE_BYTES */) { check(drt_renderer_export_frame_buffers(h_, handle_out)); }
+	void importFrameBuffers(const void* handle) { check(drt_renderer_import_frame_buffers(h_, handle)); }
+	void attachFrameBuffers(Renderer* owner) { check(drt_renderer_attach_frame_buffers(h_, owner ? owner->h_ : nullptr)); }
+	void setTuning(int32_t variant, int32_t block_threads = 0) { check(drt_renderer_set_tuning(h_, variant, block_threads)); }
 	drt_renderer* handle() const { return h_; }
 
 private:
