@@ -76,7 +76,11 @@ template <bool STRICT> struct M {
 	{
 #if defined(__CUDA_ARCH__)
 		if (STRICT) return __fdiv_rn(a, b);
-		return __fdividef(a, b);
+		// a * MUFU.RCP(b): __fdividef() adds a rescue for |b| outside [2^-126, 2^126] (FSETP + two predicated FMUL per quotient)
+		// that no divisor on this path needs (image size, 255, tonemap denominators >= 0.06, |det| >= 1e-6)
+		float r;
+		asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+		return a * r;
 #else
 		return a / b;
 #endif
@@ -98,7 +102,11 @@ template <bool STRICT> struct M {
 	{
 #if defined(__CUDA_ARCH__)
 		if (STRICT) return __fdiv_rn(1.0f, __fsqrt_rn(a));
-		return rsqrtf(a);
+		// one MUFU.RSQ: rsqrtf() wraps it in a denormal-input rescue (FSETP + two predicated FMUL) that the squared lengths on
+		// this path never need (they are sums of squares of O(1) components; a denormal one would be a zero vector anyway)
+		float r;
+		asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+		return r;
 #else
 		return 1.0f / sqrtf(a);
 #endif
@@ -107,7 +115,9 @@ template <bool STRICT> struct M {
 	{
 #if defined(__CUDA_ARCH__)
 		if (STRICT) return __fdiv_rn(1.0f, a);
-		return __fdividef(1.0f, a);
+		float r;
+		asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+		return r;
 #else
 		return 1.0f / a;
 #endif
