@@ -287,6 +287,14 @@ class Renderer:
         check(_lib.lib().drt_trace_primary(self._h, ctypes.byref(cam), scene._h, frame_index, out.ctypes.data, out.size))
         return out
 
+    def trace_primary_noalloc(self, cam, scene, frame_index=1):
+        """trace_primary through drt_trace_primary_noalloc: device staging in libdrt.so's static scratch (no cudaMalloc);
+        width * height <= NOALLOC_MAX_PIXELS."""
+        w, h = self.getBufferWidth(), self.getBufferHeight()
+        out = np.zeros(w * h, dtype=[("prim_id", np.int32), ("t", np.float32), ("u", np.float32), ("v", np.float32)])
+        check(_lib.lib().drt_trace_primary_noalloc(self._h, ctypes.byref(cam), scene._h, frame_index, out.ctypes.data, out.size))
+        return out
+
     def __del__(self):
         try:
             if self._h:

@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -897,6 +898,71 @@ extern "C" int drt_trace_primary(drt_renderer* r, const drt_camera* cam, const d
 	DRT_CUDA(launch_trace_primary(P, frame_index, r->hits.p, launch_config(r), r->stream));
 	r->kernel_launches++;
 	DRT_CUDA(cudaMemcpyAsync(out_host, r->hits.p, n * sizeof(Hit), cudaMemcpyDeviceToHost, r->stream));
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	return DRT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// allocation-free primary-ray probe (no counterpart in the reference)
+// ---------------------------------------------------------------------------------------------
+// drt_trace_primary stages the kernel's hit records in a lazily cudaMalloc'ed device buffer (r->hits). Callers that must
+// not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) get the same kernel
+// with that scratch in a file-scope device array of DRT_NOALLOC_MAX_PIXELS records (4 MiB; every GPU that loads the library
+// holds it until exit). All calls share the array and it keeps the last call's contents; the kernel overwrites every record
+// it later copies out, so nothing has to start at zero. Calls that overlap on one GPU race on it.
+static __device__ __align__(256) unsigned char g_noalloc_hits[(size_t)DRT_NOALLOC_MAX_PIXELS * sizeof(drt::Hit)];
+static_assert(sizeof(drt::Hit) == 16, "scratch size is stated in 16-byte hit records");
+
+// Names the array from device code as well, so that the symbol is kept whatever the host side does with it (and gives
+// tools a way to scrub it): sets the first n records to "miss".
+static __global__ void k_noalloc_scrub(int n)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) reinterpret_cast<int4*>(g_noalloc_hits)[i] = make_int4(-1, 0, 0, 0);
+}
+
+#define DRT_NOALLOC_MAX_DEVICES 64
+static drt::Hit* g_noalloc_ptr[DRT_NOALLOC_MAX_DEVICES]; // device address of g_noalloc_hits per device (0 = not resolved yet)
+static std::mutex g_noalloc_mutex;
+
+// In host code `g_noalloc_hits` is only a handle of the symbol, not a device address: resolve it once per device, with
+// that device current, and hand the kernel the resolved pointer.
+static int noalloc_scratch(int device, drt::Hit** out)
+{
+	if (device < 0 || device >= DRT_NOALLOC_MAX_DEVICES) return fail(DRT_ERR_INVALID, "drt_trace_primary_noalloc: device ordinal beyond the scratch table");
+	std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+	if (!g_noalloc_ptr[device]) {
+		int cur = -1;
+		DRT_CUDA(cudaGetDevice(&cur));
+		if (cur != device) return fail(DRT_ERR_CUDA, "drt_trace_primary_noalloc: the renderer's device is not current");
+		void* p = nullptr;
+		DRT_CUDA(cudaGetSymbolAddress(&p, g_noalloc_hits));
+		if (!p) return fail(DRT_ERR_CUDA, "drt_trace_primary_noalloc: cudaGetSymbolAddress returned a null address");
+		g_noalloc_ptr[device] = (drt::Hit*)p;
+	}
+	*out = g_noalloc_ptr[device];
+	return DRT_OK;
+}
+
+extern "C" int drt_trace_primary_noalloc(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, uint32_t frame_index,
+	drt_hit* out_host, size_t count)
+{
+	RenderParams P;
+	int rc = make_render_params(r, cam, scene, nullptr, P);
+	if (rc) return rc;
+	if (!out_host) return fail(DRT_ERR_INVALID, "drt_trace_primary_noalloc: null output");
+	const size_t n = (size_t)r->width * r->height;
+	if (n > (size_t)DRT_NOALLOC_MAX_PIXELS)
+		return fail(DRT_ERR_INVALID, "drt_trace_primary_noalloc: " + std::to_string(r->width) + "x" + std::to_string(r->height) + " = " + std::to_string(n) +
+			" pixels exceed the static scratch of " + std::to_string((size_t)DRT_NOALLOC_MAX_PIXELS) + " hit records (DRT_NOALLOC_MAX_PIXELS); use drt_trace_primary");
+	if (count < n) return fail(DRT_ERR_INVALID, "drt_trace_primary_noalloc: output too small");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	Hit* scratch = nullptr;
+	rc = noalloc_scratch(r->device, &scratch);
+	if (rc) return rc;
+	DRT_CUDA(launch_trace_primary(P, frame_index, scratch, launch_config(r), r->stream));
+	r->kernel_launches++;
+	DRT_CUDA(cudaMemcpyAsync(out_host, scratch, n * sizeof(Hit), cudaMemcpyDeviceToHost, r->stream));
 	DRT_CUDA(cudaStreamSynchronize(r->stream));
 	return DRT_OK;
 }

@@ -203,6 +203,19 @@ int drt_renderer_get_counters(drt_renderer* r, drt_counters* out, int reset);
 int drt_trace_primary(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, uint32_t frame_index,
 	drt_hit* out_host, size_t count);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation). Same kernel, arguments and results
+ * as drt_trace_primary, but the device-side staging of the hit records lives in a static device array inside libdrt.so
+ * instead of a lazily allocated buffer: the call performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ * Limit: width * height <= DRT_NOALLOC_MAX_PIXELS (16-byte records: 4 MiB, held by every GPU that loads the library until
+ * exit); larger renderers are rejected with DRT_ERR_INVALID. All calls share that array and it keeps the last call's
+ * contents (every record copied out is overwritten first, nothing has to be cleared): calls that overlap on one GPU --
+ * two renderers, two threads, two streams -- race on it, so serialise them. The first call on a device resolves the
+ * array's device address (cudaGetSymbolAddress, with that device current); make it before starting a graph capture. */
+#define DRT_NOALLOC_MAX_PIXELS 262144 /* = 512 x 512, BASELINE config 1 */
+int drt_trace_primary_noalloc(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, uint32_t frame_index,
+	drt_hit* out_host, size_t count);
+
 void drt_default_camera(drt_camera* out);     /* Camera.cuh:32-46 + EditorLayer.cpp:35-40 */
 void drt_default_settings(drt_settings* out); /* RendererSettings.h:22-34 */
 const char* drt_last_error(void);
