@@ -37,8 +37,10 @@ WORKLOAD = {
 }
 if os.environ.get("DRT_BENCH_SPP"):  # profiling runs under ncu only: a shorter launch of the same kernel
     WORKLOAD["spp"] = int(os.environ["DRT_BENCH_SPP"])
-CPU_SAMPLE_FRAMES = 128   # cpu_baseline leg: ~10-20 s on the GPU box's host cores
-REF_STEP_FRAMES = 32      # --impl reference: samples per pixel rendered per step (bounded sample of the 256)
+CPU_SAMPLE_FRAMES = 128   # cpu_baseline leg: at most this many of the 256 samples per pixel (~10 s on 16 host cores) ...
+CPU_SAMPLE_BUDGET_S = float(os.environ.get("DRT_CPU_BUDGET_S", "30"))   # ... and at most this much wall time
+REF_STEP_FRAMES = 1       # --impl reference: ONE of the 256 samples per pixel per step (8.1 M rays, ~70 ms on 16 cores)
+REF_BUDGET_S = float(os.environ.get("DRT_REF_BUDGET_S", "45"))          # wall budget of the whole reference arm
 SCENE_PATH = os.path.join(ROOT, "tests", "golden", "scenes", WORKLOAD["scene"])
 
 
@@ -153,13 +155,139 @@ def oracle_scene():
     return orc, orc.create(s.triangles(), mats, [s.texture(i) for i in range(s.stats()["textures"])])
 
 
-def cpu_reference_step(orc, oh, frame, frames=1, threads=0):
-    """One bounded sample of the workload on the host cores: `frames` of the 256 samples per pixel."""
+def host_threads():
+    """Threads the CPU arm may use: the affinity mask of this process (not os.cpu_count(), which ignores taskset / cgroup
+    cpusets), further limited by a cgroup CPU quota when one is set."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except Exception:
+        n = os.cpu_count() or 1
+    try:  # cgroup v2 quota: "max 100000" or "<quota> <period>"
+        q, per = open("/sys/fs/cgroup/cpu.max").read().split()[:2]
+        if q != "max":
+            n = max(1, min(n, int(float(q) / float(per) + 0.5)))
+    except Exception:
+        pass
+    return max(1, n)
+
+
+def cpu_child_main(argv):
+    """Child process of the CPU arms (`bench.py --_cpu-child frames_per_step steps warmup threads acc_path|-`): renders
+    `frames_per_step` of the 256 samples per pixel of the workload per step with the CPU checker and prints one JSON line per
+    finished step on stdout. Runs in its own process so that the parent can enforce a wall budget whatever the host does."""
+    import numpy as np
     import oracles as O
+    fps, steps, warmup, threads, acc_path = int(argv[0]), int(argv[1]), int(argv[2]), int(argv[3]), argv[4]
+    out = os.dup(1)
+    os.dup2(2, 1)  # the reference's loader prints to stdout (Scene.cu:43-54)
+
+    def say(d):
+        os.write(out, (json.dumps(d) + "\n").encode())
+
+    orc, oh = oracle_scene()
     cam = O.default_camera_bytes()
     st = O.settings_bytes(sun=WORKLOAD["sun"], bounces=WORKLOAD["bounces"], max_samples=100000)
-    _, rays, sec = orc.render(oh, cam, st, WORKLOAD["width"], WORKLOAD["height"], frame, frames, nthreads=threads)
-    return rays[0] + rays[1], sec
+    W, H = WORKLOAD["width"], WORKLOAD["height"]
+    acc = np.zeros(W * H * 3, np.float32)
+    say({"ready": True, "kind": orc.kind, "threads": threads, "omp_max_threads": orc.max_threads()})
+    frame = 1
+    for k in range(-warmup, steps):
+        if k == 0:
+            acc[:] = 0.0
+            frame = 1  # the timed steps are frame indices 1, 2, ... (what the GPU arm's first frames are)
+        _, rays, sec = orc.render(oh, cam, st, W, H, frame, fps, acc=acc, nthreads=threads)
+        frame += fps
+        say({"step": k, "rays": int(rays[0] + rays[1]), "sec": sec, "frames": fps})
+        if k >= 0 and acc_path != "-" and (k == steps - 1 or (k + 1) % 16 == 0):
+            np.save(acc_path + ".tmp.npy", acc)
+            os.replace(acc_path + ".tmp.npy", acc_path)
+            say({"saved": k + 1})
+    return 0
+
+
+def run_cpu_arm(frames_per_step, steps, warmup, budget_s, threads, acc_path=None, tag="cpu"):
+    """Runs the CPU checker in a child process under a wall budget; returns what completed:
+    {kind, threads, steps_done, rays, sec, frames, saved_frames, note}. Never raises, never outlives budget_s + 5 s."""
+    import select
+    import signal
+    res = {"kind": None, "threads": threads, "steps_done": 0, "rays": 0, "sec": 0.0, "frames": 0, "saved_frames": 0, "note": ""}
+    env = dict(os.environ)
+    env["OMP_NUM_THREADS"] = str(threads)     # torchrun exports OMP_NUM_THREADS=1
+    env.setdefault("OMP_WAIT_POLICY", "passive")  # idle team members sleep: no spin-wait pathologies on a shared / throttled host
+    env.pop("OMP_PROC_BIND", None)
+    cmd = [sys.executable, os.path.abspath(__file__), "--_cpu-child", str(frames_per_step), str(steps), str(warmup), str(threads), acc_path or "-"]
+    t0 = time.perf_counter()
+    try:
+        child = subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=None, env=env, start_new_session=True)
+    except Exception as e:
+        res["note"] = "could not start the CPU child: %s" % e
+        return res
+    old_term = None
+
+    def kill_child(*_):
+        try:
+            os.killpg(child.pid, signal.SIGKILL)  # exactly the process group started above
+        except Exception:
+            pass
+
+    def on_term(signum, frm):
+        kill_child()
+        raise KeyboardInterrupt("signal %d" % signum)
+
+    try:
+        old_term = signal.signal(signal.SIGTERM, on_term)
+    except Exception:
+        pass
+    buf = b""
+    try:
+        while True:
+            left = budget_s - (time.perf_counter() - t0)
+            if left <= 0:
+                res["note"] = "wall budget of %.0f s reached after %d of %d steps" % (budget_s, res["steps_done"], steps)
+                break
+            rd, _, _ = select.select([child.stdout], [], [], min(left, 5.0))
+            if not rd:
+                log("[%s] waiting for the CPU child (%.0f s elapsed, %d steps done, threads %d)" % (tag, time.perf_counter() - t0, res["steps_done"], threads))
+                continue
+            chunk = os.read(child.stdout.fileno(), 65536)
+            if not chunk:
+                break
+            buf += chunk
+            while b"\n" in buf:
+                ln, buf = buf.split(b"\n", 1)
+                try:
+                    d = json.loads(ln)
+                except Exception:
+                    continue
+                if "ready" in d:
+                    res["kind"] = d["kind"]
+                    log("[%s] CPU child ready after %.1f s: kind %s, threads %d (affinity %d, os.cpu_count %s, omp_get_max_threads %d)"
+                        % (tag, time.perf_counter() - t0, d["kind"], threads, len(os.sched_getaffinity(0)), os.cpu_count(), d["omp_max_threads"]))
+                elif "saved" in d:
+                    res["saved_frames"] = d["saved"] * frames_per_step
+                elif "step" in d:
+                    log("[%s] step %d: %.3f s, %.1f Mrays/s, threads %d, %.1f s elapsed" % (tag, d["step"], d["sec"], d["rays"] / max(d["sec"], 1e-9) / 1e6, threads, time.perf_counter() - t0))
+                    if d["step"] >= 0:
+                        res["steps_done"] += 1
+                        res["rays"] += d["rays"]
+                        res["sec"] += d["sec"]
+                        res["frames"] += d["frames"]
+            if res["steps_done"] >= steps and (acc_path is None or res["saved_frames"] >= res["frames"]):
+                break
+    except KeyboardInterrupt as e:
+        res["note"] = "interrupted (%s) after %d of %d steps" % (e, res["steps_done"], steps)
+    finally:
+        kill_child()
+        try:
+            child.wait(timeout=5)
+        except Exception:
+            pass
+        if old_term is not None:
+            try:
+                signal.signal(signal.SIGTERM, old_term)
+            except Exception:
+                pass
+    return res
 
 
 def ref_cuda_baseline(frames=8):
@@ -198,33 +326,43 @@ def _ref_cuda_run(L, h, frames):
 
 
 def run_reference(args, rank):
+    """--impl reference: the reference's own traversal / shade sources compiled host-side (oracle/_ref; the C port when that
+    library did not travel), all host threads of the affinity mask, ONE of the 256 samples per pixel per step, under a wall
+    budget (REF_BUDGET_S). The JSON line is emitted from a `finally`, from whatever steps completed."""
     if rank != 0:
         return 0
-    orc, oh = oracle_scene()
-    cores = os.cpu_count() or orc.max_threads()  # explicit: torchrun exports OMP_NUM_THREADS=1
-    for w in range(args.warmup):
-        cpu_reference_step(orc, oh, 1 + w * REF_STEP_FRAMES, frames=REF_STEP_FRAMES, threads=cores)
-    rays_total, sec_total = 0, 0.0
+    threads = host_threads()
     t0 = time.perf_counter()
-    for k in range(args.steps):
-        rays, sec = cpu_reference_step(orc, oh, 1 + (args.warmup + k) * REF_STEP_FRAMES, frames=REF_STEP_FRAMES, threads=cores)
-        rays_total += rays
-        sec_total += sec
-    wall = time.perf_counter() - t0
-    mrays = rays_total / sec_total / 1e6
-    samples = WORKLOAD["width"] * WORKLOAD["height"] * args.steps * REF_STEP_FRAMES / sec_total
-    sample_desc = "%d of the 256 samples per pixel of the 1920x1080 frame per step, OpenMP over rows" % REF_STEP_FRAMES
-    line = {
-        "impl": "reference", "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * sec_total / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic camera path over the bundled room scene (fixture re-muxed from the reference model)",
-        "samples_per_s": samples,
-        "config": {"workload": "room.glb 1920x1080, 8 bounces, sun shadow rays; CPU arm: %d spp per step" % REF_STEP_FRAMES, **WORKLOAD},
-        "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": cores, "kind": orc.kind, "sample": sample_desc},
-        "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "wall_s": wall,
-    }
-    emit_json_line(line)
+    res = {"kind": None, "threads": threads, "steps_done": 0, "rays": 0, "sec": 0.0, "frames": 0, "note": "not started"}
+    attempts = []
+    try:
+        warm = min(args.warmup, 2)  # (a CPU arm has nothing to warm up beyond the page cache)
+        res = run_cpu_arm(REF_STEP_FRAMES, args.steps, warm, REF_BUDGET_S, threads, tag="reference")
+        attempts.append({"threads": threads, "steps_done": res["steps_done"], "note": res["note"]})
+        if res["steps_done"] == 0 and threads > 1:
+            # nothing finished with the full team: one thread, no OpenMP team at all
+            log("[reference] no step completed with %d threads (%s); retrying single-threaded" % (threads, res["note"]))
+            res = run_cpu_arm(REF_STEP_FRAMES, args.steps, 0, REF_BUDGET_S, 1, tag="reference/1-thread")
+            attempts.append({"threads": 1, "steps_done": res["steps_done"], "note": res["note"]})
+    finally:
+        done = res["steps_done"]
+        sec = res["sec"] if done else float("nan")
+        mrays = res["rays"] / res["sec"] / 1e6 if done else 0.0
+        W, H = WORKLOAD["width"], WORKLOAD["height"]
+        sample_desc = ("%d of the 256 samples per pixel of the 1920x1080 frame per step (%.1f M rays), OpenMP over rows, %d threads; %d of %d steps completed%s"
+                       % (REF_STEP_FRAMES, res["rays"] / max(done, 1) / 1e6, res["threads"], done, args.steps, ("; " + res["note"]) if res["note"] else ""))
+        line = {
+            "impl": "reference", "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": done,
+            "steps_requested": args.steps, "warmup": min(args.warmup, 2), "ms_per_step": 1e3 * sec / max(done, 1), "higher_is_better": True,
+            "scaling": "strong" if args.scaling == "strong" else "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic camera path over the bundled room scene (fixture re-muxed from the reference model)",
+            "samples_per_s": W * H * res["frames"] / res["sec"] if done else 0.0,
+            "config": {"workload": "room.glb 1920x1080, 8 bounces, sun shadow rays (BASELINE config 3); CPU arm: %d spp per step, wall budget %.0f s" % (REF_STEP_FRAMES, REF_BUDGET_S), **WORKLOAD},
+            "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": res["threads"], "kind": res["kind"] or "none", "sample": sample_desc},
+            "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "wall_s": time.perf_counter() - t0, "attempts": attempts,
+        }
+        emit_json_line(line)
     return 0
 
 
@@ -248,6 +386,12 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     W, H, SPP = WORKLOAD["width"], WORKLOAD["height"], WORKLOAD["spp"]
+    strong = args.scaling == "strong" or args.shard in ("tiles", "p2p")
+    if strong and args.shard == "samples" and SPP % world:
+        raise SystemExit("bench.py: strong sample-range sharding needs spp (%d) divisible by the number of GPUs (%d)" % (SPP, world))
+    # samples per pixel THIS rank renders per step: strong scaling = one SPP-sample frame split over the ranks
+    rank_spp = SPP // world if (strong and args.shard == "samples") else SPP
+    frame_spp = SPP if strong else SPP * world  # samples per pixel of the frame one step produces (all GPUs together)
 
     scene = drt.Scene()
     scene.loadGLTFmodel(SCENE_PATH)
@@ -285,19 +429,19 @@ def run_ours(args, rank, world, local_rank):
     host_frame_np = host_frame.numpy()
 
     def step(e2e):
-        """reset -> one batched 256-spp launch -> (N>1: NCCL reduce) -> (rank 0: resolve) [-> host readback]"""
+        """reset -> one batched launch of this rank's share -> (N>1: NCCL reduce) -> (rank 0: resolve) [-> host readback]"""
         r.resetAccumulationBuffer()          # (p2p: rank 0 zeroes the shared buffers, the others only their sample counters)
         if p2p and world > 1:
             if rank == 0:
                 stream.synchronize()         # the shared buffers are zeroed ...
             node_barrier.wait()              # ... before anybody stores into them (host barrier in shared memory, a few us)
-        r.Render(cam, scene, SPP)            # (returns with this rank's tiles stored)
+        r.Render(cam, scene, rank_spp)       # (returns with this rank's share done: its tiles stored / its frame indices summed)
         if p2p and world > 1:
             node_barrier.wait()              # the frame (sums and display) is complete in rank 0's buffers
         elif world > 1:
             dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
-                r.resolve(SPP if tiles else SPP * world)
+                r.resolve(frame_spp)
         if e2e and rank == 0:
             r.readback(drt.DRT_RGBA32F, out=host_frame_np)
 
@@ -367,44 +511,87 @@ def run_ours(args, rank, world, local_rank):
         rays_per_launch = total_rays / args.steps / world
         achieved = (bytes_per_ray * rays_per_launch + fb_bytes) / (per_launch_ms * 1e-3) / 1e9
         ncu = ncu_capture_summary()
-        roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                    "traffic": ncu.get("traffic"), "traffic_note": ncu.get("traffic_note"), "issue": ncu.get("issue"),
-                    "peak_kind": peak_kind, "kernel": "k_render<STRICT=0,STATS=0,VARIANT=%d> (phased, one launch per step)" % max(4, int(os.environ.get("DRT_VARIANT", "4"))),
-                    "algorithmic_bytes_per_ray": bytes_per_ray, "node_visits_per_ray": V, "tri_tests_per_ray": T,
-                    "note": "scene is cache resident (42 KB): the binding roofline is SM issue rate, see profiles/ and DESIGN.md"}
-        # ---- CPU baseline: bounded sample on the host cores ----
+        algorithmic_bw = {"achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "peak_kind": peak_kind,
+                          "algorithmic_bytes_per_ray": bytes_per_ray, "node_visits_per_ray": V, "tri_tests_per_ray": T,
+                          "note": "SURVEY 8d byte formula (80 B x node visits + 48 B x triangle tests per ray + 48 B per pixel per launch); these bytes are served by L1 "
+                                  "(scene = 42 KB), so this is NOT the binding roofline -- see `traffic` for what DRAM really moves"}
+        # The binding roofline is SM issue rate x SIMT lanes: achieved = thread-level instructions per second =
+        # (thread instructions per ray of the committed ncu capture of this very launch shape) x (rays per second measured here);
+        # peak = 148 SMs x 4 schedulers x 32 lanes x the SM clock sampled during the timed region.
+        sm_mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0
+        issue_peak = 148 * 4 * 32 * sm_mhz * 1e6
+        rays_per_s = total_rays / (max_ms * 1e-3) / world   # per GPU
+        tipr = None
+        if ncu.get("thread_inst") and ncu.get("spp"):
+            capture_rays = rays_per_launch * ncu["spp"] / rank_spp   # rays are a property of the frame: proportional to the sample count
+            tipr = ncu["thread_inst"] / capture_rays
+        issue_achieved = tipr * rays_per_s if tipr else None
+        roofline = {"bound": "issue", "achieved": issue_achieved / 1e12 if issue_achieved else None, "peak": issue_peak / 1e12, "unit": "T thread-instructions/s",
+                    "frac": issue_achieved / issue_peak if issue_achieved else None,
+                    "traffic": ncu.get("traffic"), "traffic_note": ncu.get("traffic_note"),
+                    "thread_instructions_per_ray": tipr, "warp_instructions_per_ray": (ncu["warp_inst"] / capture_rays) if tipr and ncu.get("warp_inst") else None,
+                    "capture": {k: ncu.get(k) for k in ("source", "spp", "duration_ms", "issue_slot_fraction", "active_lanes_per_instruction", "local_sectors")},
+                    "peak_note": "148 SMs x 4 schedulers x 32 lanes x %.0f MHz (SM clock sampled during the timed region)" % sm_mhz,
+                    "kernel": "k_render<STRICT=0,STATS=0,VARIANT=%d> (phased, one launch per step)" % max(4, int(os.environ.get("DRT_VARIANT", "4"))),
+                    "algorithmic_bw": algorithmic_bw}
+        # ---- CPU baseline: bounded sample on the host cores (child process under a wall budget), and the parity of the GPU's
+        #      first frames of the SAME image against the frames the CPU just rendered ----
         cpu = None
-        if world == 1:  # reported baselines are measured at N=1 only (torchrun also pins OMP_NUM_THREADS=1)
-            orc, oh = oracle_scene()
-            ncores = os.cpu_count() or orc.max_threads()
-            crays, csec = cpu_reference_step(orc, oh, 1, frames=CPU_SAMPLE_FRAMES, threads=ncores)
-            cpu = {"value": crays / csec / 1e6, "unit": "Mrays/s", "cores": ncores, "kind": orc.kind,
-                   "sample": "%d of the 256 samples per pixel (frame indices 1..%d) of the same 1920x1080 frame, %.1f s"
-                             % (CPU_SAMPLE_FRAMES, CPU_SAMPLE_FRAMES, csec)}
+        parity = None
+        skip_baselines = bool(os.environ.get("DRT_BENCH_SKIP_BASELINES"))  # profiling runs under ncu
+        if world == 1 and not skip_baselines:  # reported baselines are measured at N=1 only
+            threads = host_threads()
+            acc_path = os.path.join(ROOT, "gpurun_out", "cpu_baseline_acc_%d.npy" % os.getpid())
+            os.makedirs(os.path.dirname(acc_path), exist_ok=True)
+            # steps of 8 samples per pixel, up to CPU_SAMPLE_FRAMES samples, at most CPU_SAMPLE_BUDGET_S seconds
+            res = run_cpu_arm(8, CPU_SAMPLE_FRAMES // 8, 0, CPU_SAMPLE_BUDGET_S, threads, acc_path=acc_path, tag="cpu_baseline")
+            if res["steps_done"]:
+                cpu = {"value": res["rays"] / res["sec"] / 1e6, "unit": "Mrays/s", "cores": res["threads"], "kind": res["kind"],
+                       "sample": "%d of the 256 samples per pixel (frame indices 1..%d) of the same 1920x1080 frame, %.1f s%s"
+                                 % (res["frames"], res["frames"], res["sec"], ("; " + res["note"]) if res["note"] else "")}
+            else:
+                cpu = {"value": None, "unit": "Mrays/s", "cores": threads, "kind": res["kind"], "sample": "no step completed: " + res["note"]}
+            n_par = res["saved_frames"]
+            if n_par and os.path.exists(acc_path):
+                ref_acc = np.load(acc_path).reshape(H, W, 3).astype(np.float64) / n_par
+                r.set_frame_schedule(1, 1)
+                r.resetAccumulationBuffer()
+                r.Render(cam, scene, n_par)            # production mode, the benchmarked kernel, frame indices 1..n_par
+                got = r.readback(drt.DRT_ACCUM_RGB32F).reshape(H, W, 3).astype(np.float64) / n_par
+                d = got - ref_acc
+                parity = {"spp": n_par, "rmse": float(np.sqrt((d * d).mean())), "mean_diff": float(d.mean()), "max_abs_diff": float(np.abs(d).max()),
+                          "pixels_differing": float((np.abs(d).max(axis=2) > 0).mean()),
+                          "what": "display values (LDR, [0,1]) of the GPU's production-mode render of frame indices 1..%d of the benchmarked 1080p image "
+                                  "against the CPU reference's render of the same frame indices (same seeds)" % n_par}
+            try:
+                os.remove(acc_path)
+            except OSError:
+                pass
         value = total_rays / (max_ms * 1e-3) / 1e6
         refcuda = None
         try:
-            if world == 1:
+            if world == 1 and not skip_baselines:
                 refcuda = ref_cuda_baseline()
         except Exception as e:  # measurement aid only
             refcuda = {"error": str(e)}
         if refcuda and "error" not in refcuda:
-            rays_per_sample = total_rays / args.steps / world / SPP   # same workload: rays are a property of the frame
+            rays_per_sample = total_rays / args.steps / world / rank_spp   # same workload: rays are a property of the frame
             for v in refcuda.values():
                 v["Mrays_s_at_our_ray_count"] = rays_per_sample / (v["ms_per_sample"] * 1e-3) / 1e6
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": max_ms / args.steps, "higher_is_better": True, "scaling": "strong" if tiles else "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": max_ms / args.steps, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic camera path over the bundled room scene (fixture re-muxed from the reference model)",
-            "samples_per_s": W * H * SPP * (1 if tiles else world) * args.steps / (max_ms * 1e-3),
-            "config": {"workload": "room.glb 1920x1080, %d spp per %s per step, 8 bounces, sun shadow rays (BASELINE config 3)" % (SPP, "frame (all GPUs together)" if tiles else "GPU"),
+            "samples_per_s": W * H * frame_spp * args.steps / (max_ms * 1e-3),
+            "config": {"workload": "room.glb 1920x1080, %d spp per %s per step, 8 bounces, sun shadow rays (BASELINE config 3)" % (SPP, "frame (all GPUs together)" if strong else "GPU"),
                        **WORKLOAD, "parallelism": ("image-tile sharding x%d (8x4 tiles, interleaved), peer stores into rank 0's frame buffers over NVLink, no collective (host barrier in shared memory)" if p2p
                                                    else "image-tile sharding x%d (8x4 tiles, interleaved) + NCCL reduce of the accumulation buffer" if tiles
                                                    else "sample-range sharding x%d + NCCL reduce of the accumulation buffer") % world,
+                       "spp_per_gpu_per_step": rank_spp, "spp_per_frame": frame_spp,
                        "l2": "256 MB buffer written between timed steps (L2 flush)", "wide_nodes": sstats["wide_nodes"],
                        "build_ms": sstats["build_ms"]},
             "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 152, "d2h_bytes_per_step": W * H * 16},
-            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "parity": parity,
             "reference_cuda_on_this_gpu": refcuda,
             "rays_per_step": total_rays / args.steps, "wall_s_timed_region": t_wall,
         }
@@ -418,16 +605,23 @@ def run_ours(args, rank, world, local_rank):
 
 
 def ncu_capture_summary():
-    """DRAM bytes per launch and issue statistics of the render kernel from the committed `ncu --set full` capture
-    (profiles/rNN*_render_phased_raw.txt, latest; the capture itself is never part of a timed run)."""
+    """Counters of the render kernel from the latest committed ncu capture (profiles/rNN*_render_phased_raw.txt, written by
+    tools/ncu_raw.py from a capture of `bench.py --steps 1`; its header says which launch: `spp=<n>`). The capture itself
+    is never part of a timed run."""
     import glob
+    import re
     found = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_render_phased_raw.txt")))
     if not found:
         return {}
     path = found[-1]  # the latest capture of the default kernel
     vals = {}
+    spp = None
     for line in open(path):
-        if " = " in line and not line.startswith("#"):
+        if line.startswith("#"):
+            m = re.search(r"spp=(\d+)", line) or re.search(r"DRT_BENCH_SPP=(\d+)", line)
+            if m:
+                spp = int(m.group(1))
+        elif " = " in line:
             k, v = line.rsplit(" = ", 1)
             name, _, unit = k.partition(" [")
             try:
@@ -435,19 +629,29 @@ def ncu_capture_summary():
             except ValueError:
                 pass
     scale = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
-    out = {}
+    out = {"source": os.path.relpath(path, ROOT), "spp": spp}
     if "dram__bytes_read.sum" in vals and "dram__bytes_write.sum" in vals:
         out["traffic"] = sum(vals[k][0] * scale.get(vals[k][1], 1.0) for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
-        out["traffic_note"] = ("bytes per launch, dram read+write of one k_render launch under ncu --set full (16-spp launch; "
-                               "a launch touches each frame-buffer pixel once whatever its sample count)")
-    if "smsp__issue_active.avg.pct_of_peak_sustained_active" in vals:
-        out["issue"] = {"issue_slot_fraction": vals["smsp__issue_active.avg.pct_of_peak_sustained_active"][0] / 100.0,
-                        "active_lanes_per_instruction": vals.get("smsp__thread_inst_executed_per_inst_executed.ratio", (None,))[0],
-                        "source": os.path.relpath(path, ROOT)}
+        out["traffic_note"] = ("bytes per launch, dram read+write of one k_render launch under ncu (%s-spp launch; "
+                               "a launch touches each frame-buffer pixel once whatever its sample count)" % spp)
+    get = lambda k: vals[k][0] if k in vals else None
+    out["thread_inst"] = get("smsp__thread_inst_executed.sum")
+    out["warp_inst"] = get("smsp__inst_executed.sum")
+    out["duration_ms"] = get("gpu__time_duration.sum")
+    if get("smsp__issue_active.avg.pct_of_peak_sustained_active") is not None:
+        out["issue_slot_fraction"] = get("smsp__issue_active.avg.pct_of_peak_sustained_active") / 100.0
+    out["active_lanes_per_instruction"] = get("smsp__thread_inst_executed_per_inst_executed.ratio")
+    if out["thread_inst"] is None and out["warp_inst"] and out["active_lanes_per_instruction"]:
+        out["thread_inst"] = out["warp_inst"] * out["active_lanes_per_instruction"]
+    ld, st = get("l1tex__t_sectors_pipe_lsu_mem_local_op_ld.sum"), get("l1tex__t_sectors_pipe_lsu_mem_local_op_st.sum")
+    if ld is not None and st is not None:
+        out["local_sectors"] = ld + st
     return out
 
 
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "--_cpu-child":
+        return cpu_child_main(sys.argv[2:])
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -456,6 +660,9 @@ def main():
     ap.add_argument("--shard", default=os.environ.get("DRT_SHARD", "samples"), choices=["samples", "tiles", "p2p"],
                     help="N>1: sample-range sharding (weak scaling, default), image-tile sharding of each frame + reduce (strong scaling), "
                          "or image tiles stored directly into rank 0's buffers over NVLink (p2p)")
+    ap.add_argument("--scaling", default=os.environ.get("DRT_SCALING", "strong"), choices=["strong", "weak"],
+                    help="N>1 with sample-range sharding: strong (default) = ONE 256-spp frame, 256/N samples per pixel per GPU + reduce + resolve; "
+                         "weak = 256 spp per GPU (a 256*N-spp frame per step)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -469,7 +676,7 @@ def main():
         # convenience: re-launch under torchrun
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus), "--master-addr", "127.0.0.1",
                "--master-port", os.environ.get("MASTER_PORT", "29511"), os.path.abspath(__file__), "--gpus", str(args.gpus),
-               "--steps", str(args.steps), "--warmup", str(args.warmup), "--shard", args.shard]
+               "--steps", str(args.steps), "--warmup", str(args.warmup), "--shard", args.shard, "--scaling", args.scaling]
         return subprocess.call(cmd)
     return run_ours(args, rank, world, local_rank)
 
