@@ -103,6 +103,7 @@ SIGNATURES = {
     "drt_renderer_resolve": (_i, [_vp, _u]),
     "drt_renderer_get_counters": (_i, [_vp, _P(drt_counters), _i]),
     "drt_trace_primary": (_i, [_vp, _P(drt_camera), _vp, _u, _vp, _sz]),
+    "drt_trace_rays": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _vp]),
     "drt_trace_primary_noalloc": (_i, [_vp, _P(drt_camera), _vp, _u, _vp, _sz]),
     "drt_default_camera": (None, [_P(drt_camera)]),
     "drt_default_settings": (None, [_P(drt_settings)]),

@@ -287,6 +287,15 @@ class Renderer:
         check(_lib.lib().drt_trace_primary(self._h, ctypes.byref(cam), scene._h, frame_index, out.ctypes.data, out.size))
         return out
 
+    def trace_rays(self, scene, origins, directions, anyhit=False):
+        """Ray-level parity probe (drt_trace_rays): structured array (prim_id, t, u, v) per ray."""
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(directions, np.float32).reshape(-1, 3)
+        assert o.shape == d.shape
+        out = np.zeros(o.shape[0], dtype=[("prim_id", np.int32), ("t", np.float32), ("u", np.float32), ("v", np.float32)])
+        check(_lib.lib().drt_trace_rays(self._h, scene._h, o.ctypes.data, d.ctypes.data, o.shape[0], 1 if anyhit else 0, out.ctypes.data))
+        return out
+
     def trace_primary_noalloc(self, cam, scene, frame_index=1):
         """trace_primary through drt_trace_primary_noalloc: device staging in libdrt.so's static scratch (no cudaMalloc);
         width * height <= NOALLOC_MAX_PIXELS."""

@@ -902,6 +902,28 @@ extern "C" int drt_trace_primary(drt_renderer* r, const drt_camera* cam, const d
 	return DRT_OK;
 }
 
+extern "C" int drt_trace_rays(drt_renderer* r, const drt_scene* scene, const float* origins, const float* directions, size_t n_rays,
+	int anyhit, drt_hit* out_host)
+{
+	if (!r || !scene) return fail(DRT_ERR_INVALID, "drt_trace_rays: null argument");
+	if (!scene->built) return fail(DRT_ERR_INVALID, "drt_trace_rays: call drt_scene_build_bvh first");
+	if (scene->device != r->device) return fail(DRT_ERR_INVALID, "drt_trace_rays: scene was built on another device");
+	if (n_rays == 0) return DRT_OK;
+	if (!origins || !directions || !out_host) return fail(DRT_ERR_INVALID, "drt_trace_rays: null ray or output array");
+	if (n_rays > 0x7fffffffu / 3) return fail(DRT_ERR_INVALID, "drt_trace_rays: too many rays");
+	if (renderer_bind(r)) return DRT_ERR_CUDA;
+	DevBuf<float> d_o, d_d;
+	DevBuf<Hit> d_h;
+	DRT_CUDA(d_o.alloc(3 * n_rays)); DRT_CUDA(d_d.alloc(3 * n_rays)); DRT_CUDA(d_h.alloc(n_rays));
+	DRT_CUDA(cudaMemcpyAsync(d_o.p, origins, 3 * n_rays * sizeof(float), cudaMemcpyHostToDevice, r->stream));
+	DRT_CUDA(cudaMemcpyAsync(d_d.p, directions, 3 * n_rays * sizeof(float), cudaMemcpyHostToDevice, r->stream));
+	DRT_CUDA(launch_trace_rays(scene->view, d_o.p, d_d.p, (int)n_rays, anyhit != 0, d_h.p, launch_config(r), r->stream));
+	r->kernel_launches++;
+	DRT_CUDA(cudaMemcpyAsync(out_host, d_h.p, n_rays * sizeof(Hit), cudaMemcpyDeviceToHost, r->stream));
+	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	return DRT_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // allocation-free primary-ray probe (no counterpart in the reference)
 // ---------------------------------------------------------------------------------------------

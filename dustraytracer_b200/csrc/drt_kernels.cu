@@ -180,6 +180,48 @@ __global__ void __launch_bounds__(256) k_trace_primary(const __grid_constant__ R
 	flush_counters(P.counters, pc, &ts);
 }
 
+// Ray-level parity probe (drt_trace_rays): caller-given rays through the SAME resumable steps the phased render kernels run
+// (node_step_f32 / node_step_q8 + tri_step / tri_step2 + trav_advance, drt_phased.cuh), one ray per thread, serial schedule.
+// anyhit = RayTest semantics (TraceRay.cu:35-38: first accepted hit ends the ray), else TraceRay closest hit.
+template <bool STRICT, int FMT, bool TRI2>
+__global__ void __launch_bounds__(128) k_trace_rays(const SceneView sc, const float* __restrict__ org, const float* __restrict__ dir, int n, bool anyhit, Hit* out)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const V3 o = mk3(org[3 * (size_t)i], org[3 * (size_t)i + 1], org[3 * (size_t)i + 2]);
+	const V3 d = mk3(dir[3 * (size_t)i], dir[3 * (size_t)i + 1], dir[3 * (size_t)i + 2]);
+	LaneTrav L;
+	LaneStack K;
+	RayBox R;
+	ray_box_setup(o, d, R);
+	trav_begin(L, FLT_MAX);
+	int phase = sc.num_nodes > 0 ? PH_NODE : PH_SHADE;
+	bool occluded = false;
+	while (phase != PH_SHADE) {
+		if (phase == PH_NODE) {
+			if (FMT == NODE_FMT_F32) node_step_f32<false>(sc.nodes_f32, L, K, R, nullptr);
+			else node_step_q8<false>(sc.nodes, L, K, R, nullptr);
+			phase = trav_advance(L, K);
+		}
+		else {
+			if (TRI2 ? tri_step2<STRICT, false>(sc, sc.tris, L, o, d, anyhit, nullptr) : tri_step<STRICT, false>(sc, sc.tris, L, o, d, anyhit, nullptr)) {
+				occluded = true;
+				phase = PH_SHADE;
+			}
+			else phase = trav_advance(L, K);
+		}
+	}
+	(void)occluded;
+	Hit h;
+	h.prim = -1; h.t = -1.f; h.u = 0.f; h.v = 0.f;
+	if (L.hit.prim >= 0) {
+		const V2 bc = hit_barycentrics<STRICT>(sc.tris, L.hit.prim, o, d); // the operations of tri_step: the same bits
+		h.prim = (int32_t)as_uint(ld_f4(sc.tris + 3 * (size_t)L.hit.prim).w);
+		h.t = L.hit.t; h.u = bc.x; h.v = bc.y;
+	}
+	out[i] = h;
+}
+
 __global__ void k_resolve(float4* display, const float4* accum, int n, float total)
 {
 	int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -474,6 +516,19 @@ cudaError_t launch_trace_primary(const RenderParams& P, uint32_t frame_index, Hi
 	const unsigned blocks = (unsigned)((tiles + wpb - 1) / wpb);
 	if (cfg.strict) k_trace_primary<true><<<blocks, threads, 0, s>>>(P, frame_index, out_dev, cfg.rtl, wpb);
 	else k_trace_primary<false><<<blocks, threads, 0, s>>>(P, frame_index, out_dev, cfg.rtl, wpb);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_trace_rays(const SceneView& sc, const float* org_dev, const float* dir_dev, int n, bool anyhit, Hit* out_dev, const LaunchConfig& cfg, cudaStream_t s)
+{
+	if (n <= 0) return cudaSuccess;
+	const unsigned blocks = (unsigned)((n + 127) / 128);
+	const bool f32 = sc.nodes_f32 != nullptr && cfg.variant != 3 && cfg.variant != 7 && cfg.variant != 8 && cfg.variant != 10 && cfg.variant != 14;
+	const bool tri2 = cfg.variant == 15 || (cfg.auto_variant && sc.num_tris >= DRT_TRI2_MIN_TRIS);
+#define DRT_TR(S, F, T2) k_trace_rays<S, F, T2><<<blocks, 128, 0, s>>>(sc, org_dev, dir_dev, n, anyhit, out_dev)
+	if (cfg.strict) { if (f32) { if (tri2) DRT_TR(true, NODE_FMT_F32, true); else DRT_TR(true, NODE_FMT_F32, false); } else { if (tri2) DRT_TR(true, NODE_FMT_Q8, true); else DRT_TR(true, NODE_FMT_Q8, false); } }
+	else { if (f32) { if (tri2) DRT_TR(false, NODE_FMT_F32, true); else DRT_TR(false, NODE_FMT_F32, false); } else { if (tri2) DRT_TR(false, NODE_FMT_Q8, true); else DRT_TR(false, NODE_FMT_Q8, false); } }
+#undef DRT_TR
 	return cudaGetLastError();
 }
 

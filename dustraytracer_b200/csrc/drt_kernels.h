@@ -33,6 +33,7 @@ cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* i
 cudaError_t launch_expand_nodes(const WideNode* wide, drt_f4* out_f32, int n, cudaStream_t s);
 cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches);
 cudaError_t launch_trace_primary(const RenderParams& P, uint32_t frame_index, Hit* out_dev, const LaunchConfig& cfg, cudaStream_t s);
+cudaError_t launch_trace_rays(const SceneView& sc, const float* org_dev, const float* dir_dev, int n, bool anyhit, Hit* out_dev, const LaunchConfig& cfg, cudaStream_t s);
 cudaError_t launch_resolve(drt_f4* display, const drt_f4* accum, int n_pixels, float total_samples, cudaStream_t s);
 cudaError_t launch_pack_rgba8(uint32_t* out, const drt_f4* display, int n_pixels, cudaStream_t s);
 cudaError_t launch_pack_rgb32f(float* out, const drt_f4* accum, int n_pixels, cudaStream_t s);

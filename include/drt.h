@@ -203,6 +203,16 @@ int drt_renderer_get_counters(drt_renderer* r, drt_counters* out, int reset);
 int drt_trace_primary(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, uint32_t frame_index,
 	drt_hit* out_host, size_t count);
 
+/* Ray-level parity probe: n_rays caller-given rays (origins / directions: 3 floats each, host memory; directions as the path
+ * would pass them, not normalised) through the very step functions the render kernels run (wide-node slab test, Moller-Trumbore
+ * in the reference's operation order, alpha cut-out). anyhit = 0: TraceRay closest hit (Kernel/TraceRay.cu:15-33 ->
+ * BVH/BVHTraversal.cuh:14-73); anyhit != 0: RayTest (TraceRay.cu:35-38 -> BVHTraversal.cuh:76-134), which ignores the hit
+ * interval and ends at the first accepted triangle (prim_id >= 0 means "occluded"; WHICH triangle depends on the tree).
+ * Replaces nothing the editor calls: it exists so that the reference's Intersection.cu:4-36 edge cases (ray in the triangle's
+ * plane, |det| at the epsilon, t below epsilon, hits on edges) can be pushed through the CUDA code one ray at a time. */
+int drt_trace_rays(drt_renderer* r, const drt_scene* scene, const float* origins, const float* directions, size_t n_rays,
+	int anyhit, drt_hit* out_host);
+
 /* No counterpart in the reference: added for callers that cannot call cudaMalloc
  * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation). Same kernel, arguments and results
  * as drt_trace_primary, but the device-side staging of the hit records lives in a static device array inside libdrt.so

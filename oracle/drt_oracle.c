@@ -630,6 +630,52 @@ void orc_trace_primary(void* h, const void* cam88, int W, int H, unsigned framei
 		}
 }
 
+/* Camera rays as RayGen issues them for `frameidx` (RayGen.cuh:65-78 -> Camera.cu:82-123): out_od6[p] = origin xyz, direction xyz,
+ * p = x + y*W. rtl = argument evaluation order of the g++-compiled reference (1) or nvcc's (0). */
+void orc_camera_rays(const void* cam88, int W, int H, unsigned frameidx, int rtl, float* out_od6)
+{
+	Camera cam; memcpy(&cam, cam88, sizeof(cam));
+	for (int y = 0; y < H; y++)
+		for (int x = 0; x < W; x++) {
+			f2 uv; uv.x = ((float)x / (uint32_t)W) * 2 - 1; uv.y = ((float)y / (uint32_t)H) * 2 - 1;
+			uint32_t seed = (uint32_t)x + (uint32_t)y * (uint32_t)W;
+			seed *= frameidx;
+			Ray ray = camera_get_ray(&cam, uv, (float)(uint32_t)W, (float)(uint32_t)H, &seed, rtl);
+			float* o = out_od6 + 6 * ((size_t)x + (size_t)y * W);
+			o[0] = ray.o.x; o[1] = ray.o.y; o[2] = ray.o.z; o[3] = ray.d.x; o[4] = ray.d.y; o[5] = ray.d.z;
+		}
+}
+
+/* Tree-free checker for big soups: closest hit of every ray over ALL triangles with the reference's Moller-Trumbore
+ * (Intersection.cu:4-36, `intersection` above), no BVH, no box test. Among equal t the lowest triangle index wins (the rule the
+ * CUDA path documents; the reference itself keeps the first one its own tree order meets, BVHTraversal.cuh:51).
+ * tris9: n x (v0, v1, v2); rays: origin xyz + direction xyz. prim = -1 / t = -1 on a miss; u = UVW.y, v = UVW.z. */
+void orc_brute_force_closest(const float* tris9, int n, const float* rays_od6, int nrays, int* prim, float* t, float* u, float* v, int nthreads)
+{
+#ifdef _OPENMP
+	if (nthreads > 0) omp_set_num_threads(nthreads);
+#endif
+#pragma omp parallel for schedule(dynamic, 16)
+	for (int r = 0; r < nrays; r++) {
+		const float* od = rays_od6 + 6 * (size_t)r;
+		Ray ray = make_ray(mk3(od[0], od[1], od[2]), mk3(od[3], od[4], od[5]));
+		int best = -1;
+		float bt = FLT_MAX;
+		f3 buvw = mk3(0, 0, 0);
+		for (int i = 0; i < n; i++) {
+			const float* p = tris9 + 9 * (size_t)i;
+			float ti;
+			f3 uvw;
+			if (!intersection(&ray, mk3(p[0], p[1], p[2]), mk3(p[3], p[4], p[5]), mk3(p[6], p[7], p[8]), &ti, &uvw)) continue;
+			if (ti < bt) { bt = ti; best = i; buvw = uvw; } /* ascending i: an equal t keeps the lower index */
+		}
+		prim[r] = best;
+		t[r] = best >= 0 ? bt : -1.f;
+		u[r] = best >= 0 ? buvw.y : 0.f;
+		v[r] = best >= 0 ? buvw.z : 0.f;
+	}
+}
+
 /* RenderKernel.cu:20-35 + Renderer.cu:80-117: accumulates frames [begin, begin+count) into acc (W*H*3).
  * Returns seconds in the pixel loops; counters[0] = TraceRay calls, counters[1] = RayTest calls. */
 double orc_render(void* h, const void* cam88, const void* settings64, int W, int H, unsigned frame_begin, unsigned frame_count,

@@ -198,6 +198,24 @@ class PortOracle:
         self.L.orc_trace_primary(h, P(cam), W, H, frameidx, P(pid), P(t), P(u), P(v), nthreads)
         return pid, t, u, v
 
+    def camera_rays(self, cam, W, H, frameidx=1, rtl=True):
+        """Primary rays as RayGen issues them: [W*H, 6] origin xyz, direction xyz (Camera.cu:82-123)."""
+        out = np.zeros((W * H, 6), np.float32)
+        self.L.orc_camera_rays(P(cam), W, H, frameidx, int(rtl), P(out))
+        return out
+
+    def brute_force_closest(self, tris9, rays_od6, nthreads=0):
+        """Closest hit of every ray over ALL triangles with the reference's Moller-Trumbore, no tree (lowest index wins ties)."""
+        tris9 = np.ascontiguousarray(tris9, np.float32).reshape(-1, 9)
+        rays = np.ascontiguousarray(rays_od6, np.float32).reshape(-1, 6)
+        n = rays.shape[0]
+        pid = np.zeros(n, np.int32)
+        t = np.zeros(n, np.float32)
+        u = np.zeros_like(t)
+        v = np.zeros_like(t)
+        self.L.orc_brute_force_closest(P(tris9), tris9.shape[0], P(rays), n, P(pid), P(t), P(u), P(v), nthreads)
+        return pid, t, u, v
+
     def render(self, h, cam, settings, W, H, frame_begin=1, frames=1, acc=None, nthreads=0):
         if acc is None:
             acc = np.zeros(W * H * 3, np.float32)
@@ -300,3 +318,42 @@ class HostEmu:
 
 def best_oracle():
     return RefOracle() if RefOracle.available() else PortOracle()
+
+
+def pcg_hash_np(v):
+    """Random.cu:6-11 on uint32 arrays."""
+    v = v.astype(np.uint32)
+    with np.errstate(over="ignore"):
+        state = v * np.uint32(747796405) + np.uint32(2891336453)
+        word = ((state >> ((state >> np.uint32(28)) + np.uint32(4))) ^ state) * np.uint32(277803737)
+    return (word >> np.uint32(22)) ^ word
+
+
+def soup_triangles(n, seed=0x0D057A11):
+    """SURVEY.md 8d synthetic random-triangle soup (BASELINE config 5): counter-based generator on the reference's pcg_hash,
+    centres uniform in [-50, 50]^3, vertices within +-0.25 of the centre. The same function as tools/run_configs.py soup()."""
+    out = np.empty((n, 9), np.float32)
+    chunk = 1 << 20
+    for a in range(0, n, chunk):
+        i = np.arange(a, min(n, a + chunk), dtype=np.uint32)
+        base = pcg_hash_np(np.uint32(seed) ^ i)
+        with np.errstate(over="ignore"):
+            r = np.stack([pcg_hash_np(base * np.uint32(12) + np.uint32(k)) for k in range(12)], 1).astype(np.float64) / 4294967296.0
+        c = r[:, 0:3] * 100.0 - 50.0
+        for j in range(3):
+            out[a:a + len(i), 3 * j:3 * j + 3] = (c + (r[:, 3 + 3 * j:6 + 3 * j] - 0.5) * 0.5).astype(np.float32)
+    return out
+
+
+def oracle_scene_for(name_or_path, orc=None):
+    """(oracle, handle) of the strongest checker for a bundled scene: the reference's own loader + builder when its library
+    travelled, else the C port fed by the product's HOST loader (triangle / material / texel CRCs are pinned in test_abi)."""
+    orc = orc or best_oracle()
+    path = name_or_path if os.path.sep in name_or_path else scene_path(name_or_path)
+    if orc.kind == "reference":
+        return orc, orc.load(path)
+    import dustraytracer_b200 as d
+    s = d.Scene()
+    s.loadGLTFmodel(path)
+    mats = np.frombuffer(b"".join(bytes(m) for m in s.materials()), np.uint32).reshape(-1, 11).copy()
+    return orc, orc.create(s.triangles(), mats, [s.texture(i) for i in range(s.stats()["textures"])])

@@ -1,0 +1,272 @@
+"""Round-2 parity cases of the CUDA path (through the C ABI), closing the gaps the round-1 review named:
+
+  * the reference-generated known-answer vectors (Moller-Trumbore edge cases, tests/golden/kat.npz, made by tools/make_golden.py
+    from the reference's own Intersection.cu) pushed THROUGH THE CUDA CODE one ray at a time (drt_trace_rays);
+  * the thin-lens camera branch (Camera.cu:98-115, random_in_unit_disk) on the GPU;
+  * BASELINE config 5 (synthetic soup) against a TREE-FREE checker: brute-force closest hit over all triangles with the
+    reference's Moller-Trumbore, and a 4-spp image against the C port given the same triangles;
+  * BASELINE configs 2 and 4 at their full 1920x1080 size, whole accumulated images bit for bit;
+  * production mode (the benchmarked one): the difference to the oracle must average down like 1/sqrt(spp) with no bias floor.
+
+Bars: bit-exact (uint32 compare) in STRICT mode; production mode as stated per test. Needs a B200: -m gpu.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import oracles as O
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(O.ROOT, "tests", "golden")
+STRICT = 1 | 2  # DRT_FLAG_STRICT | DRT_FLAG_HOST_ARG_ORDER (the oracle is g++-compiled)
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def drt():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import dustraytracer_b200 as d
+    return d
+
+
+_scene_cache = {}
+
+
+def gpu_scene(drt, name):
+    if name not in _scene_cache:
+        s = drt.Scene()
+        s.loadGLTFmodel(O.scene_path(name))
+        drt.BVHBuilder().buildIterative(s)
+        _scene_cache[name] = s
+    return _scene_cache[name]
+
+
+def camera_from(drt, cam_f32):
+    import ctypes
+    cam = drt.Camera()
+    ctypes.memmove(ctypes.addressof(cam), np.ascontiguousarray(cam_f32, np.float32).tobytes(), 88)
+    return cam
+
+
+def settings_from(drt, st_bytes):
+    import ctypes
+    st = drt.RendererSettings()
+    ctypes.memmove(ctypes.addressof(st), st_bytes.tobytes(), 64)
+    return st
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# (c) reference KATs through CUDA
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("variant", [4, 3, 15])  # expanded nodes, compressed nodes, two-triangle TRI step
+def test_moller_trumbore_kats_through_cuda(drt, variant):
+    """Every mt_* case of kat.npz (ray in the triangle's plane, |det| around 1e-6, t below epsilon, hits on an edge / the
+    hypotenuse / a vertex, a degenerate triangle, 52 random ones) as a one-triangle scene: hit decision, t, u, v must be the
+    reference's bits (Intersection.cu:4-36); any-hit mode must make the same decision (RayTest, no alpha here)."""
+    k = np.load(os.path.join(GOLDEN, "kat.npz"))
+    r = drt.Renderer(flags=STRICT)
+    r.set_tuning(variant, 0)
+    rp = drt.Renderer()           # production arithmetic
+    rp.set_tuning(variant, 0)
+    n_hit = 0
+    for i in range(len(k["mt_hit"])):
+        s = drt.Scene.from_triangles(k["mt_tri"][i].reshape(1, 9))
+        s.build_bvh()
+        o, d = k["mt_o"][i], k["mt_d"][i]
+        h = r.trace_rays(s, o, d)[0]
+        a = r.trace_rays(s, o, d, anyhit=True)[0]
+        want = int(k["mt_hit"][i])
+        assert (h["prim_id"] >= 0) == bool(want), (i, h, want)
+        assert (a["prim_id"] >= 0) == bool(want), (i, a, want)
+        if want:
+            n_hit += 1
+            assert h["prim_id"] == 0 and a["prim_id"] == 0
+            got = np.array([h["t"], h["u"], h["v"]], np.float32)
+            ref = np.array([k["mt_t"][i], k["mt_uvw"][i][1], k["mt_uvw"][i][2]], np.float32)
+            assert np.array_equal(bits(got), bits(ref)), (i, got, ref)
+            # production arithmetic (FMA contraction, MUFU reciprocal): same decision away from the predicate's boundaries
+            uvw = k["mt_uvw"][i]
+            if uvw.min() > 1e-3 and k["mt_t"][i] > 1e-3:
+                p = rp.trace_rays(s, o, d)[0]
+                assert p["prim_id"] == 0 and abs(p["t"] - k["mt_t"][i]) <= 1e-5 * abs(k["mt_t"][i]) + 1e-7, (i, p)
+    assert 5 <= n_hit < len(k["mt_hit"])
+
+
+def test_trace_rays_equals_the_primary_probe_and_handles_edge_inputs(drt):
+    scene = gpu_scene(drt, "animemaid")  # alpha cut-outs on the path
+    port = O.PortOracle()
+    W, H = 160, 90
+    cam = O.default_camera_bytes()
+    rays = port.camera_rays(cam, W, H, 3, rtl=True)
+    r = drt.Renderer(flags=STRICT)
+    r.ResizeBuffer(W, H)
+    prim = r.trace_primary(camera_from(drt, cam), scene, 3)
+    got = r.trace_rays(scene, rays[:, 0:3], rays[:, 3:6])
+    assert np.array_equal(bits(np.frombuffer(got.tobytes(), np.uint32)), bits(np.frombuffer(prim.tobytes(), np.uint32)))
+    occl = r.trace_rays(scene, rays[:, 0:3], rays[:, 3:6], anyhit=True)
+    assert np.array_equal(occl["prim_id"] >= 0, prim["prim_id"] >= 0)  # camera rays: occluded <=> a closest hit exists
+    # empty input, empty scene
+    assert r.trace_rays(scene, np.zeros((0, 3), np.float32), np.zeros((0, 3), np.float32)).size == 0
+    e = drt.Scene.from_triangles(np.zeros((0, 9), np.float32))
+    e.build_bvh()
+    assert (r.trace_rays(e, rays[:7, 0:3], rays[:7, 3:6])["prim_id"] == -1).all()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# (a6) thin lens
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("variant", [4, 9, 1])
+def test_thin_lens_camera_on_the_gpu(drt, variant):
+    """defocus_angle = 2 degrees: Camera::GetRay takes the random_in_unit_disk branch (Camera.cu:98-115, Random.cu:60-66).
+    Primary hits and a whole accumulated image must be the oracle's bits."""
+    cam_f = O.default_camera_bytes()
+    cam_f[5] = 2.0
+    W, H, frames = 96, 54, 4
+    st_b = O.settings_bytes(sun=True, bounces=3)
+    orc, oh = O.oracle_scene_for("room")
+    pid, t, u, v = orc.trace_primary(oh, cam_f, W, H, 5)
+    ref, rays, _ = orc.render(oh, cam_f, st_b, W, H, 1, frames)
+    orc.free(oh)
+    scene = gpu_scene(drt, "room")
+    r = drt.Renderer(flags=STRICT)
+    r.set_tuning(variant, 0)
+    r.m_RendererSettings = settings_from(drt, st_b)
+    r.ResizeBuffer(W, H)
+    cam = camera_from(drt, cam_f)
+    hits = r.trace_primary(cam, scene, 5)
+    assert np.array_equal(hits["prim_id"], pid)
+    assert np.array_equal(bits(hits["t"]), bits(t)) and np.array_equal(bits(hits["u"]), bits(u)) and np.array_equal(bits(hits["v"]), bits(v))
+    r.counters(reset=True)
+    r.Render(cam, scene, frames)
+    acc = r.readback(drt.DRT_ACCUM_RGB32F).reshape(-1)
+    assert np.array_equal(bits(acc), bits(ref)), "max abs diff %g" % np.abs(acc - ref).max()
+    c = r.counters()
+    assert (c["closest_rays"], c["shadow_rays"]) == (rays[0], rays[1])
+    # and the lens really is on: the pin-hole image differs
+    cam0 = camera_from(drt, O.default_camera_bytes())
+    r.resetAccumulationBuffer()
+    r.Render(cam0, scene, frames)
+    assert not np.array_equal(bits(r.readback(drt.DRT_ACCUM_RGB32F).reshape(-1)), bits(ref))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# (b) config 5: synthetic soup against a tree-free checker
+# ---------------------------------------------------------------------------------------------------------------------
+def test_soup_100k_against_brute_force_and_the_port(drt):
+    n, W, H = 100000, 160, 90
+    tris = O.soup_triangles(n)
+    port = O.PortOracle()
+    cam_f = O.default_camera_bytes()
+    rays = port.camera_rays(cam_f, W, H, 1, rtl=True)
+    pid, t, u, v = port.brute_force_closest(tris, rays)   # 1.44 G Moller-Trumbore tests, OpenMP
+    assert 0.05 < (pid >= 0).mean() < 1.0
+    s = drt.Scene.from_triangles(tris)
+    s.build_bvh()
+    cam = camera_from(drt, cam_f)
+    for variant in (4, 3, 15):
+        r = drt.Renderer(flags=STRICT)
+        r.set_tuning(variant, 0)
+        r.ResizeBuffer(W, H)
+        hits = r.trace_primary(cam, s, 1)
+        assert np.array_equal(hits["prim_id"], pid), (variant, int((hits["prim_id"] != pid).sum()))
+        assert np.array_equal(bits(hits["t"]), bits(t)) and np.array_equal(bits(hits["u"]), bits(u)) and np.array_equal(bits(hits["v"]), bits(v))
+        got = r.trace_rays(s, rays[:, 0:3], rays[:, 3:6])
+        assert np.array_equal(got["prim_id"], pid) and np.array_equal(bits(got["t"]), bits(t))
+        st = r.counters()
+        assert st["max_stack"] <= 32
+    # production arithmetic: the same triangles except near-ties, which are logged
+    rp = drt.Renderer()
+    rp.ResizeBuffer(W, H)
+    hp = rp.trace_primary(cam, s, 1)
+    diff = hp["prim_id"] != pid
+    near = np.abs(hp["t"] - t) <= 1e-4 * np.abs(t)
+    print("soup-100k production mode: %d of %d primary ids differ from the brute-force checker (all near-ties: %s)" % (diff.sum(), diff.size, bool(near[diff].all())))
+    assert diff.mean() <= 2e-5 + 1.0 / diff.size and near[diff & (pid >= 0) & (hp["prim_id"] >= 0)].all()
+    # a 4-spp image (4 bounces, sun shadow rays: incoherent secondary rays through the whole soup) against the C port given the
+    # same triangles -- the port traverses ITS tree (the reference's builder restated), we traverse ours
+    st_b = O.settings_bytes(sun=True, bounces=4)
+    mats = np.frombuffer(b"".join(bytes(m) for m in s.materials()), np.uint32).reshape(-1, 11).copy()
+    oh = port.create(s.triangles(), mats, [])
+    ref, rays_n, _ = port.render(oh, cam_f, st_b, W, H, 1, 4)
+    port.free(oh)
+    r = drt.Renderer(flags=STRICT)
+    r.m_RendererSettings = settings_from(drt, st_b)
+    r.ResizeBuffer(W, H)
+    r.Render(cam, s, 4)
+    acc = r.readback(drt.DRT_ACCUM_RGB32F).reshape(-1)
+    c = r.counters()
+    nd = int((bits(acc) != bits(ref)).sum())
+    print("soup-100k 4 spp: %d of %d accumulation words differ; rays ours %d+%d, port %d+%d" % (nd, acc.size, c["closest_rays"], c["shadow_rays"], rays_n[0], rays_n[1]))
+    assert nd == 0 and (c["closest_rays"], c["shadow_rays"]) == (rays_n[0], rays_n[1])
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# (d) configs 2 and 4 at full size
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,sun,bounces", [("dense_monkey", False, 4), ("valorant_ghost", True, 2), ("animemaid", True, 2)])
+def test_full_size_images_bit_exact(drt, name, sun, bounces):
+    """BASELINE config 2 (dense_monkey, 4 bounces) and config 4 (valorant_ghost / animemaid, textured, alpha-masked any-hit) at
+    1920x1080: two frames accumulated, every float of the sum equal to the oracle's, ray counts equal."""
+    W, H, frames = 1920, 1080, 2
+    cam_f = O.default_camera_bytes()
+    st_b = O.settings_bytes(sun=sun, bounces=bounces)
+    orc, oh = O.oracle_scene_for(name)
+    ref, rays, sec = orc.render(oh, cam_f, st_b, W, H, 1, frames)
+    orc.free(oh)
+    scene = gpu_scene(drt, name)
+    r = drt.Renderer(flags=STRICT)  # automatic kernel selection: what a caller gets
+    r.m_RendererSettings = settings_from(drt, st_b)
+    r.ResizeBuffer(W, H)
+    r.Render(camera_from(drt, cam_f), scene, frames)
+    acc = r.readback(drt.DRT_ACCUM_RGB32F).reshape(-1)
+    c = r.counters()
+    nd = int((bits(acc) != bits(ref)).sum())
+    print("%s 1080p x %d frames: %d differing words, %d + %d rays, %s oracle %.1f s" % (name, frames, nd, c["closest_rays"], c["shadow_rays"], orc.kind, sec))
+    assert nd == 0
+    assert (c["closest_rays"], c["shadow_rays"]) == (rays[0], rays[1])
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# (a) production mode: no bias floor
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,sun,bounces", [("room", True, 8), ("animemaid", True, 2), ("dense_monkey", False, 4)])
+def test_production_mode_has_no_bias_floor(drt, name, sun, bounces):
+    """The benchmarked mode (flags 0: FMA contraction, MUFU rcp / rsqrt, nvcc argument order is NOT used here -- the oracle's
+    order is kept so that both sides draw the same random numbers) against the oracle at 64 ... 4096 spp on the same seeds.
+    A path that diverges after a rounding difference is a fresh, unbiased sample of the same estimator, so the difference
+    image must average down like 1/sqrt(spp): RMSE(4096) / RMSE(64) = 0.125 within 25 %, and the mean signed difference at
+    4096 spp must be below 1e-3 LDR units (a bias of a few 1e-3 is what the round-1 test could not see)."""
+    W, H = 96, 54
+    spps = [64, 256, 1024, 4096]
+    cam_f = O.default_camera_bytes()
+    st_b = O.settings_bytes(sun=sun, bounces=bounces, max_samples=1 << 30)
+    orc, oh = O.oracle_scene_for(name)
+    scene = gpu_scene(drt, name)
+    r = drt.Renderer(flags=2)  # production arithmetic, oracle's argument order
+    r.m_RendererSettings = settings_from(drt, st_b)
+    r.ResizeBuffer(W, H)
+    cam = camera_from(drt, cam_f)
+    ref = np.zeros(W * H * 3, np.float32)
+    done = 0
+    rmse, bias = {}, {}
+    for spp in spps:
+        orc.render(oh, cam_f, st_b, W, H, done + 1, spp - done, acc=ref)
+        r.Render(cam, scene, spp - done)
+        done = spp
+        got = r.readback(drt.DRT_ACCUM_RGB32F).reshape(-1).astype(np.float64) / spp
+        d = got - ref.astype(np.float64) / spp
+        rmse[spp] = float(np.sqrt((d * d).mean()))
+        bias[spp] = float(d.mean())
+    orc.free(oh)
+    ratio = rmse[4096] / rmse[64]
+    print("%s production vs %s oracle: RMSE %s, mean diff %s, RMSE(4096)/RMSE(64) = %.4f" % (
+        name, orc.kind, {k: "%.2e" % v for k, v in rmse.items()}, {k: "%+.1e" % v for k, v in bias.items()}, ratio))
+    assert rmse[64] <= 0.02
+    assert 0.125 * 0.75 <= ratio <= 0.125 * 1.25
+    assert abs(bias[4096]) <= 1e-3

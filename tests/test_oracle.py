@@ -126,3 +126,32 @@ def test_port_equals_reference_live(port, name, sun, bounces):
     assert np.array_equal(bits(ra), bits(pa)) and rr == pr
     R.free(rh)
     port.free(ph)
+
+
+def test_port_camera_rays_match_the_reference_kats(port):
+    """orc_camera_rays against the camera vectors tools/make_golden.py took from the reference's Camera::GetRay
+    (pin-hole and thin-lens cases, Camera.cu:82-123)."""
+    k = np.load(os.path.join(GOLDEN, "kat.npz"))
+    for (x, y, W, H, f, defocus), ray in zip(k["cam_cases"], k["cam_rays"]):
+        cam = k["cam_defocus"] if defocus else k["cam_default"]
+        r = port.camera_rays(cam, int(W), int(H), int(f), rtl=True)
+        assert np.array_equal(bits(r[x + y * W]), bits(ray))
+
+
+@pytest.mark.parametrize("name", ["cube", "room", "cornell_box"])
+def test_brute_force_checker_agrees_with_the_tree(port, name):
+    """The tree-free checker used for the soups (orc_brute_force_closest) against the port's own BVH traversal (itself pinned to
+    the reference's golden hits): same t, u, v bits; the id may differ only where two triangles are hit at exactly the same t
+    (the tree keeps the first it meets, the checker the lowest index)."""
+    h, tris, mats, tex = _port_scene(port, name)
+    cam = O.default_camera_bytes()
+    W, H = 64, 36
+    pid, t, u, v = port.trace_primary(h, cam, W, H, 2)
+    rays = port.camera_rays(cam, W, H, 2, rtl=True)
+    tri9 = np.ascontiguousarray(tris.reshape(-1, 32)[:, [4, 5, 6, 12, 13, 14, 20, 21, 22]])
+    bid, bt, bu, bv = port.brute_force_closest(tri9, rays)
+    assert np.array_equal(bits(bt), bits(t))
+    same = bid == pid
+    assert same.mean() > 0.99
+    assert np.array_equal(bits(bu[same]), bits(u[same])) and np.array_equal(bits(bv[same]), bits(v[same]))
+    port.free(h)
