@@ -72,6 +72,7 @@ SIGNATURES = {
     "drt_scene_load_gltf_ex": (_i, [ctypes.c_char_p, ctypes.c_uint32, _P(_vp)]),
     "drt_scene_from_triangles": (_i, [_vp, _vp, _vp, _sz, _vp, _sz, _P(_vp)]),
     "drt_scene_add_texture": (_i, [_vp, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, _vp]),
+    "drt_decode_image": (_i, [_vp, _sz, _P(ctypes.c_int32), _P(ctypes.c_int32), _P(ctypes.c_int32), _vp, _sz]),
     "drt_scene_build_bvh": (_i, [_vp, _P(drt_bvh_params), _i]),
     "drt_scene_get_stats": (_i, [_vp, _P(drt_scene_stats)]),
     "drt_scene_get_triangles": (_i, [_vp, _vp, _sz]),

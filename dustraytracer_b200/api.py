@@ -166,6 +166,16 @@ class Scene:
             pass
 
 
+def decode_image(data):
+    """stbi_load_from_memory(data, len, &w, &h, &comps, 0) of the reference (Texture.cu:21-30): [H, W, C] uint8."""
+    buf = bytes(data)
+    w, h, c = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
+    check(_lib.lib().drt_decode_image(buf, len(buf), ctypes.byref(w), ctypes.byref(h), ctypes.byref(c), None, 0))
+    out = np.zeros((h.value, w.value, c.value), np.uint8)
+    check(_lib.lib().drt_decode_image(buf, len(buf), None, None, None, out.ctypes.data, out.nbytes))
+    return out
+
+
 class BVHBuilder:
     """class BVHBuilder (Core/BVH/BVHBuilder.cuh:12-23). Both entry points run the GPU binned-SAH build and
     emit compressed 8-wide nodes; the two knobs are kept for call compatibility (see drt_bvh_params)."""

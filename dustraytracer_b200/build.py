@@ -26,7 +26,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC,-fno-fast-math,-ffp-contract=off",
 ]
 CUDA_SOURCES = ["drt_kernels.cu", "drt_api.cu"]
-HOST_SOURCES = ["drt_gltf.cpp", "drt_gltf_robust.cpp", "drt_png.cpp"]
+HOST_SOURCES = ["drt_gltf.cpp", "drt_gltf_robust.cpp", "drt_png.cpp", "drt_jpeg.cpp"]
 
 
 def _host_cxx():

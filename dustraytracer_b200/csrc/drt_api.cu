@@ -131,6 +131,7 @@ struct drt_renderer {
 	void* ipc_display = nullptr;
 	DevBuf<Counters> counters;
 	DevBuf<unsigned> work_queue; // pixel-queue kernel: next tile, warps that have left (the kernel leaves both at zero)
+	DevBuf<uint8_t> rg_overflow; // regrouping kernel (variant 16): traversal-stack overflow area, allocated at its first launch
 	DevBuf<Hit> hits;
 	DevBuf<uint8_t> staging;
 	uint32_t frame_index = 1;   // the reference's m_FrameIndex (Renderer.hpp:41): next frame to render
@@ -294,6 +295,22 @@ int drt_scene_get_texture(const drt_scene* scene, int32_t index, int32_t* width,
 	if (comps) *comps = t.comps;
 	if (pixels_or_null) {
 		if (bytes < t.pixels.size()) return fail(DRT_ERR_INVALID, "drt_scene_get_texture: buffer too small");
+		memcpy(pixels_or_null, t.pixels.data(), t.pixels.size());
+	}
+	return DRT_OK;
+}
+
+int drt_decode_image(const uint8_t* data, size_t len, int32_t* width, int32_t* height, int32_t* comps, uint8_t* pixels_or_null, size_t bytes)
+{
+	if (!data || !len) return fail(DRT_ERR_INVALID, "drt_decode_image: null input");
+	HostTexture t;
+	std::string err;
+	if (!decode_image(data, len, t, err)) return fail(DRT_ERR_FORMAT, "drt_decode_image: " + err);
+	if (width) *width = t.width;
+	if (height) *height = t.height;
+	if (comps) *comps = t.comps;
+	if (pixels_or_null) {
+		if (bytes < t.pixels.size()) return fail(DRT_ERR_INVALID, "drt_decode_image: buffer too small");
 		memcpy(pixels_or_null, t.pixels.data(), t.pixels.size());
 	}
 	return DRT_OK;
@@ -563,7 +580,7 @@ extern "C" int drt_renderer_set_flags(drt_renderer* r, uint32_t flags)
 extern "C" int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads)
 {
 	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: null renderer");
-	if (variant < -1 || variant > 15 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
+	if (variant < -1 || variant > 16 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
 	r->auto_variant = variant < 0;
 	r->variant = variant < 0 ? 4 : variant; r->block_threads = block_threads;
 	return DRT_OK;
@@ -702,6 +719,7 @@ static int make_render_params(drt_renderer* r, const drt_camera* cam, const drt_
 	P.accum = fb_accum(r); P.display = fb_display(r); P.counters = r->counters.p;
 	P.work_queue = r->work_queue.p;
 	P.tile_first = r->tile_first; P.tile_stride = r->tile_stride;
+	P.rg_overflow = r->rg_overflow.p;
 	return DRT_OK;
 }
 
@@ -799,6 +817,10 @@ extern "C" int drt_renderer_render(drt_renderer* r, const drt_camera* cam, const
 	P.n_samples = n;
 	P.total_samples = (float)(r->samples_done + n); // = the frame index the reference divides by (RenderKernel.cu:30)
 	LaunchConfig cfg = launch_config(r);
+	if (cfg.variant == 16 && !r->rg_overflow.p) { // (a one-off: entries beyond the shared-memory part of the regrouping kernel's stacks)
+		DRT_CUDA(r->rg_overflow.alloc(regroup_overflow_bytes(r->sm_count)));
+		P.rg_overflow = r->rg_overflow.p;
+	}
 	bool probing = false;
 	const int candidate = autotune_pick(r, scene, P, probing);
 	if (candidate >= 0) autotune_apply(candidate, n, cfg);

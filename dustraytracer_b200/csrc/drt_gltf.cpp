@@ -172,14 +172,14 @@ int load_gltf(const char* path, HostScene& out, std::string& err, unsigned flags
 		std::string perr;
 		int bv = img.get_int("bufferView", -1);
 		bool ok = false;
-		if (bv >= 0 && (size_t)bv < views.size()) ok = decode_png(bdata[views[bv].buffer] + views[bv].offset, views[bv].length, tex, perr);
+		if (bv >= 0 && (size_t)bv < views.size()) ok = decode_image(bdata[views[bv].buffer] + views[bv].offset, views[bv].length, tex, perr);
 		else if (img.has("uri")) {
 			std::vector<uint8_t> bytes;
-			if (load_uri(base_dir, img.get_str("uri"), bytes)) ok = decode_png(bytes.data(), bytes.size(), tex, perr);
+			if (load_uri(base_dir, img.get_str("uri"), bytes)) ok = decode_image(bytes.data(), bytes.size(), tex, perr);
 			else perr = "cannot load image " + img.get_str("uri");
 		}
 		else perr = "image without bufferView/uri";
-		if (!ok && robust) { // e.g. JPEG: keep the slot so image indices stay stable, detach the materials that use it
+		if (!ok && robust) { // undecodable image: keep the slot so image indices stay stable, detach the materials that use it
 			out.warnings.push_back("image " + std::to_string(i) + " not decoded (" + perr + "); materials using it fall back to their factor");
 			image_ok[i] = false;
 			tex = HostTexture();

@@ -31,6 +31,11 @@ struct HostScene {
 };
 
 bool decode_png(const uint8_t* data, size_t len, HostTexture& out, std::string& err);
+// drt_jpeg.cpp: baseline / progressive JPEG with stb_image 2.29's arithmetic (the reference's decoder, Texture.cu:21-30)
+bool looks_like_jpeg(const uint8_t* data, size_t len);
+bool decode_jpeg(const uint8_t* data, size_t len, HostTexture& out, std::string& err);
+// An embedded image of any supported container (what the reference hands to stbi_load_from_memory): PNG or JPEG by signature.
+bool decode_image(const uint8_t* data, size_t len, HostTexture& out, std::string& err);
 // Loads .glb / .gltf with the reference loader's semantics (Scene.cu:22-317).
 // flags = drt_load_flags: DRT_LOAD_ROBUST switches to the spec-conforming ingest (drt_gltf_robust.cpp).
 int load_gltf(const char* path, HostScene& out, std::string& err, unsigned flags = 0);

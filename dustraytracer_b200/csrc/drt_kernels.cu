@@ -27,6 +27,7 @@
 #include "drt_kernels.h"
 #include "drt_shade.cuh"
 #include "drt_phased.cuh"
+#include "drt_regroup.cuh"
 
 namespace drt {
 
@@ -152,6 +153,57 @@ __global__ void __launch_bounds__(128, (CV == 1 || CV == 3 || CV == 4 || CV == 6
 			P.work_queue[1] = 0u;
 		}
 	}
+}
+
+// Variant 16: block-level regrouping of path contexts (drt_regroup.cuh). Persistent grid of DRT_RG_BLOCKS_PER_SM blocks per SM,
+// DRT_RG_CTX contexts per block in (dynamic) shared memory; pixels come from P.work_queue[0], which the last block to leave resets.
+template <bool STRICT, int FMT, bool TRI2>
+__global__ void __launch_bounds__(DRT_RG_THREADS, DRT_RG_BLOCKS_PER_SM) k_render_regroup(const __grid_constant__ RenderParams P, const bool rtl)
+{
+	extern __shared__ uint4 rg_smem[];
+	__shared__ unsigned tail[16];
+	__shared__ alignas(16) uint8_t lut[DRT_PERMUTE_LUT_BYTES];
+	PathCounters pc;
+	pc.closest = 0; pc.shadow = 0;
+	uint2* ovf = P.rg_overflow ? (uint2*)P.rg_overflow + (size_t)blockIdx.x * DRT_RG_CTX * DRT_PSTACK : nullptr;
+	render_block_regroup<STRICT, FMT, TRI2>(P, rtl, ovf, (uint32_t*)rg_smem, tail, lut, pc);
+	flush_counters(P.counters, pc, nullptr);
+	if (threadIdx.x == 0) {
+		__threadfence();
+		if (atomicAdd(P.work_queue + 1, 1u) == gridDim.x - 1u) {
+			P.work_queue[0] = 0u;
+			P.work_queue[1] = 0u;
+		}
+	}
+}
+
+template <bool STRICT, int FMT, bool TRI2>
+cudaError_t launch_regroup_k(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s)
+{
+	static bool configured = false;
+	if (!configured) {
+		const cudaError_t e = cudaFuncSetAttribute(k_render_regroup<STRICT, FMT, TRI2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DRT_RG_SMEM_BYTES);
+		if (e != cudaSuccess) return e;
+		configured = true;
+	}
+	const long long all_tiles = (long long)((P.width + 7) / 8) * ((P.height + 3) / 4);
+	const long long tiles = all_tiles > P.tile_first ? (all_tiles - P.tile_first + P.tile_stride - 1) / P.tile_stride : 0;
+	long long blocks = (long long)cfg.resident_sms * DRT_RG_BLOCKS_PER_SM;
+	const long long need = (tiles * 32 + DRT_RG_CTX - 1) / DRT_RG_CTX;
+	if (blocks > need) blocks = need;
+	if (blocks <= 0) return cudaSuccess;
+	k_render_regroup<STRICT, FMT, TRI2><<<(unsigned)blocks, DRT_RG_THREADS, DRT_RG_SMEM_BYTES, s>>>(P, cfg.rtl);
+	return cudaGetLastError();
+}
+
+template <bool STRICT>
+cudaError_t launch_regroup(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s)
+{
+	const bool q8 = P.scene.nodes_f32 == nullptr;
+	const bool tri2 = !q8 && P.scene.num_tris >= DRT_TRI2_MIN_TRIS;
+	if (q8) return launch_regroup_k<STRICT, NODE_FMT_Q8, false>(P, cfg, s);
+	if (tri2) return launch_regroup_k<STRICT, NODE_FMT_F32, true>(P, cfg, s);
+	return launch_regroup_k<STRICT, NODE_FMT_F32, false>(P, cfg, s);
 }
 
 template <bool STRICT>
@@ -447,6 +499,11 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 		return cudaGetLastError();
 	}
 	if (variant >= 2 && P.shade.render_mode != DRT_RENDER_NORMAL) variant = 1;
+	// variant 16: block-level regrouping (no statistics build of it: counted launches run the per-warp voting kernel)
+	if (variant == 16) {
+		if (!STATS && P.work_queue != nullptr && cfg.resident_sms > 0 && P.tile_stride > 0 && P.width < 65536 && P.height < 65536) return launch_regroup<STRICT>(P, cfg, s);
+		variant = 4;
+	}
 	// variants 9 / 10: persistent warps with a pixel queue, for launches of few samples (the reference's interactive pattern is
 	// one per launch); the renderer's auto-tuner (drt_api.cu) picks between them and variant 4 by measurement.
 	if (variant >= 9 && variant <= 14) {
@@ -500,6 +557,8 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 }
 
 } // namespace
+
+size_t regroup_overflow_bytes(int sms) { return (size_t)sms * DRT_RG_BLOCKS_PER_SM * DRT_RG_CTX * DRT_PSTACK * sizeof(uint2); }
 
 cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches)
 {

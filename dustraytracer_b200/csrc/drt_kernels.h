@@ -29,6 +29,8 @@ struct LaunchConfig {
 	int resident_sms = 0;  // SM count of the device (grid of the persistent kernel)
 };
 
+// Bytes of the regrouping kernel's traversal-stack overflow area for a device of `sms` multiprocessors (RenderParams::rg_overflow).
+size_t regroup_overflow_bytes(int sms);
 cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s);
 cudaError_t launch_expand_nodes(const WideNode* wide, drt_f4* out_f32, int n, cudaStream_t s);
 cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches);

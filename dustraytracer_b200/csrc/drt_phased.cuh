@@ -92,7 +92,11 @@ struct RayBox {
 	uint32_t oct_inv;
 };
 
-DRT_HD void ray_box_setup(V3 o, V3 d, RayBox& R)
+// `id3`, when given, receives the unscaled reciprocals (R.idn* = id * (1 - 1e-6), R.idf* = id * (1 + 1e-6)): kernels that park
+// a ray outside registers keep these 3 words instead of the 6 scaled ones and re-derive both with the same two multiplies.
+#define DRT_BOX_KN 0.999999f
+#define DRT_BOX_KF 1.000001f
+DRT_HD void ray_box_setup(V3 o, V3 d, RayBox& R, float* id3 = nullptr)
 {
 	const float tiny = 1e-20f;
 	const float dx = fabsf(d.x) > tiny ? d.x : (d.x < 0.f ? -tiny : tiny);
@@ -100,7 +104,8 @@ DRT_HD void ray_box_setup(V3 o, V3 d, RayBox& R)
 	const float dz = fabsf(d.z) > tiny ? d.z : (d.z < 0.f ? -tiny : tiny);
 	const float idx = fast_rcp(dx), idy = fast_rcp(dy), idz = fast_rcp(dz);
 	R.oct_inv = (d.x >= 0.f ? 4u : 0u) | (d.y >= 0.f ? 2u : 0u) | (d.z >= 0.f ? 1u : 0u);
-	const float kn = 0.999999f, kf = 1.000001f, ka = 4.8e-7f;
+	const float kn = DRT_BOX_KN, kf = DRT_BOX_KF, ka = 4.8e-7f;
+	if (id3) { id3[0] = idx; id3[1] = idy; id3[2] = idz; }
 	R.idnx = idx * kn; R.idny = idy * kn; R.idnz = idz * kn;
 	R.idfx = idx * kf; R.idfy = idy * kf; R.idfz = idz * kf;
 	const float ex = fabsf(o.x * idx) * ka, ey = fabsf(o.y * idy) * ka, ez = fabsf(o.z * idz) * ka;
@@ -121,8 +126,13 @@ struct LaneTrav {
 #define DRT_PSTACK 32
 #endif
 
+// Traversal stack of one lane. The step functions below are templates over the stack type so that the same code runs with
+// the stack in per-thread local memory (LaneStack, the default), in shared memory (drt_regroup.cuh) or wherever a kernel
+// keeps it; a stack type provides put(i, x, y) / get(i, x, y) for 0 <= i < DRT_PSTACK.
 struct LaneStack {
 	uint32_t x[DRT_PSTACK], y[DRT_PSTACK];
+	DRT_HD void put(int i, uint32_t vx, uint32_t vy) { x[i] = vx; y[i] = vy; }
+	DRT_HD void get(int i, uint32_t& vx, uint32_t& vy) const { vx = x[i]; vy = y[i]; }
 };
 
 DRT_HD void trav_begin(LaneTrav& L, float tmax)
@@ -134,7 +144,8 @@ DRT_HD void trav_begin(LaneTrav& L, float tmax)
 }
 
 // Phase of a lane after a NODE or TRI step (pops the stack when the current group is exhausted).
-DRT_HD int trav_advance(LaneTrav& L, LaneStack& S)
+template <class STACK>
+DRT_HD int trav_advance(LaneTrav& L, STACK& S)
 {
 	const bool has_tri = L.tri_bits != 0u, has_node = L.ng_bits > 0x00ffffffu;
 	int phase = has_tri ? PH_TRI : PH_NODE;
@@ -144,15 +155,15 @@ DRT_HD int trav_advance(LaneTrav& L, LaneStack& S)
 			// entries beyond the stack were dropped when pushed (counted via max_stack): skip them in one step
 			const int sp = L.sp - 1;
 			L.sp = sp < DRT_PSTACK - 1 ? sp : DRT_PSTACK - 1;
-			L.ng_base = S.x[L.sp]; L.ng_bits = S.y[L.sp];
+			S.get(L.sp, L.ng_base, L.ng_bits);
 		}
 	}
 	return phase;
 }
 
 // Picks the nearest pending inner child of the current group (octant order) and returns its node index.
-template <bool STATS>
-DRT_HD uint32_t trav_pop_child(LaneTrav& L, LaneStack& S, uint32_t oct_inv, TraceStats* st)
+template <bool STATS, class STACK>
+DRT_HD uint32_t trav_pop_child(LaneTrav& L, STACK& S, uint32_t oct_inv, TraceStats* st)
 {
 	const int bit = hi_bit(L.ng_bits);
 	L.ng_bits &= ~(1u << bit);
@@ -160,7 +171,7 @@ DRT_HD uint32_t trav_pop_child(LaneTrav& L, LaneStack& S, uint32_t oct_inv, Trac
 	const uint32_t rel = (uint32_t)pop_count(L.ng_bits & 0xffu & ((1u << slot) - 1u));
 	const uint32_t node_index = L.ng_base + rel;
 	if (L.ng_bits > 0x00ffffffu) {
-		if (L.sp < DRT_PSTACK) { S.x[L.sp] = L.ng_base; S.y[L.sp] = L.ng_bits; }
+		if (L.sp < DRT_PSTACK) S.put(L.sp, L.ng_base, L.ng_bits);
 		++L.sp;
 		if (STATS && st && (uint32_t)L.sp > st->max_stack) st->max_stack = (uint32_t)L.sp;
 	}
@@ -207,8 +218,8 @@ DRT_HD uint32_t permuted_child_bits(uint32_t m, uint32_t oct_inv, const uint8_t*
 	}
 
 // NODE step on expanded nodes. `nodes` may point to global or shared memory.
-template <bool STATS>
-DRT_HD void node_step_f32(const drt_f4* nodes, LaneTrav& L, LaneStack& S, const RayBox& R, TraceStats* st, const uint8_t* lut = nullptr)
+template <bool STATS, class STACK>
+DRT_HD void node_step_f32(const drt_f4* nodes, LaneTrav& L, STACK& S, const RayBox& R, TraceStats* st, const uint8_t* lut = nullptr)
 {
 	const uint32_t node_index = trav_pop_child<STATS>(L, S, R.oct_inv, st);
 	const drt_f4* np = nodes + (size_t)DRT_F32NODE_F4 * node_index;
@@ -255,8 +266,8 @@ DRT_HD float byte_to_float(uint32_t w, int i)
 }
 
 // NODE step on the builder's compressed nodes (same box arithmetic as trace_ray_mode, drt_trace.cuh).
-template <bool STATS>
-DRT_HD void node_step_q8(const drt_u4* nodes, LaneTrav& L, LaneStack& S, const RayBox& R, TraceStats* st, const uint8_t* lut = nullptr)
+template <bool STATS, class STACK>
+DRT_HD void node_step_q8(const drt_u4* nodes, LaneTrav& L, STACK& S, const RayBox& R, TraceStats* st, const uint8_t* lut = nullptr)
 {
 	const uint32_t node_index = trav_pop_child<STATS>(L, S, R.oct_inv, st);
 	const drt_u4* np = nodes + 5 * (size_t)node_index;

@@ -136,6 +136,10 @@ int drt_scene_from_triangles(const float* pos, const float* uv, const int32_t* m
 	const drt_material* materials, size_t n_materials, drt_scene** out);
 /* Appends an 8-bit texture (comps = 1..4) to a scene made by drt_scene_from_triangles. */
 int drt_scene_add_texture(drt_scene* scene, int32_t width, int32_t height, int32_t comps, const uint8_t* pixels);
+/* The image decoder of the loader on its own: replaces stbi_load_from_memory(data, len, &w, &h, &comps, 0) (Texture.cu:21-30,
+ * stb_image 2.29): PNG and JPEG (baseline and progressive), 8 bits per channel out, the file's own channel count (JPEG: 3, or 1
+ * for grey), stb's bytes. pixels_or_null = NULL asks for the size only. Host only, no GPU needed. */
+int drt_decode_image(const uint8_t* data, size_t len, int32_t* width, int32_t* height, int32_t* comps, uint8_t* pixels_or_null, size_t bytes);
 int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* params_or_null, int device);
 int drt_scene_get_stats(const drt_scene* scene, drt_scene_stats* out);
 /* Host copy of the triangle soup in load order, in the reference's 128-byte Triangle layout (Triangle.cuh:7-19). */

@@ -644,6 +644,85 @@ void emu_warp_sim3(void* h, const drt_camera* cam, const drt_settings* st, int W
 	out[8] += pc.closest + pc.shadow;
 }
 
+// Design tool for the multi-context kernel (render_warp_dual, drt_dual.cuh): one warp whose lanes each own J pixels (contexts;
+// context j of lane l = pixel l of tile (tile_x + j, tile_y)). Per iteration the warp votes for the step the most LANES can
+// run (a lane can run a step if any of its contexts waits for it), each such lane advances ONE context, sticky re-issue as
+// in the shipped kernel. pol[0..2] weights, pol[3] = minimum lanes for SHADE unless nothing else can run, pol[6..8] sticky.
+// out as in emu_warp_sim3 (issues 0..2, lane-steps 3..5, votes 6, sticky ballots 7, rays 8, worst draws 9).
+void emu_warp_sim_multi(void* h, const drt_camera* cam, const drt_settings* st, int W, int H, int tile_x, int tile_y, unsigned first,
+	unsigned n, int J, const float* pol, unsigned long long* out)
+{
+	EmuScene* s = (EmuScene*)h;
+	RenderParams P = make_params(s, cam, st, W, H);
+	P.frame_first = first; P.frame_stride = 1; P.n_samples = n;
+	struct Ctx { LanePath S; LaneTrav L; LaneStack K; RayBox R; int phase; uint32_t x, y; };
+	std::vector<Ctx> ctx(32 * J);
+	PathCounters pc; pc.closest = pc.shadow = 0;
+	TraceStats ts; memset(&ts, 0, sizeof(ts));
+	const int first_phase = P.scene.num_nodes > 0 ? PH_NODE : PH_SHADE;
+	for (int j = 0; j < J; j++)
+		for (int l = 0; l < 32; l++) {
+			Ctx& A = ctx[j * 32 + l];
+			A.x = (tile_x + j) * 8 + (l & 7); A.y = tile_y * 4 + (l >> 3);
+			A.S.acc = mk3(0, 0, 0); A.S.k = 0; A.S.fn = mk3(0, 0, 0);
+			A.phase = PH_DONE;
+			trav_begin(A.L, FLT_MAX);
+			if ((int)A.x < W && (int)A.y < H && n > 0) {
+				path_begin_sample<false>(P, A.x, A.y, false, A.S);
+				ray_box_setup(A.S.o, A.S.d, A.R);
+				A.phase = first_phase;
+			}
+		}
+	auto lanes_wanting = [&](int k) { int c = 0; for (int l = 0; l < 32; l++) { bool w = false; for (int j = 0; j < J; j++) w |= ctx[j * 32 + l].phase == k; c += w; } return c; };
+	auto run_step = [&](int pick) -> unsigned long long {
+		unsigned long long worst = 0;
+		for (int l = 0; l < 32; l++) {
+			int sel = -1;
+			for (int j = 0; j < J && sel < 0; j++) if (ctx[j * 32 + l].phase == pick) sel = j;
+			if (sel < 0) continue;
+			Ctx& A = ctx[sel * 32 + l];
+			out[3 + pick]++;
+			if (pick == PH_NODE) { node_step_f32<true>(P.scene.nodes_f32, A.L, A.K, A.R, &ts); A.phase = trav_advance(A.L, A.K); }
+			else if (pick == PH_TRI) {
+				if (tri_step<false, true>(P.scene, P.scene.tris, A.L, A.S.o, A.S.d, A.S.shadow, &ts)) A.phase = PH_SHADE;
+				else A.phase = trav_advance(A.L, A.K);
+			}
+			else {
+				const uint32_t seed0 = A.S.seed;
+				const bool more = shade_step<false, true>(P, A.x, A.y, false, A.L.hit, A.S, pc, &ts);
+				unsigned long long draws = 0; uint32_t q = seed0;
+				while (q != A.S.seed && draws < 4096) { q = pcg_hash(q); draws++; }
+				if (draws < 4096 && draws > worst) worst = draws;
+				if (!more) A.phase = PH_DONE;
+				else { ray_box_setup(A.S.o, A.S.d, A.R); trav_begin(A.L, FLT_MAX); A.phase = first_phase; }
+			}
+		}
+		return worst;
+	};
+	for (;;) {
+		int c[3];
+		for (int k = 0; k < 3; k++) c[k] = lanes_wanting(k);
+		if (c[0] + c[1] + c[2] == 0) break;
+		out[6]++;
+		int pick = -1;
+		float best = -1.f;
+		for (int k = 0; k < 3; k++) {
+			if (c[k] == 0) continue;
+			if (k == PH_SHADE && c[k] < pol[3] && c[0] + c[1] > 0) continue;
+			if (c[k] * pol[k] > best) { best = c[k] * pol[k]; pick = k; }
+		}
+		for (;;) {
+			out[pick]++;
+			const unsigned long long worst = run_step(pick);
+			if (pick == PH_SHADE) out[9] += worst;
+			const int again = lanes_wanting(pick);
+			out[7]++;
+			if (again < pol[6 + pick] || again == 0) break;
+		}
+	}
+	out[8] += pc.closest + pc.shadow;
+}
+
 void emu_camera_params(const drt_camera* cam, int W, int H, float* out20)
 {
 	CameraParams c = make_camera_params(*cam, W, H);

@@ -10,7 +10,7 @@ import pytest
 import oracles as O
 
 GOLDEN = os.path.join(O.ROOT, "tests", "golden")
-SCENES = ["cornell_box", "room", "dense_monkey", "valorant_ghost", "animemaid", "mc_transparency_test", "bvhsplit_test", "cube"]
+SCENES = ["cornell_box", "room", "dense_monkey", "valorant_ghost", "animemaid", "mc_transparency_test", "bvhsplit_test", "cube", "sunshadow_test"]
 
 
 @pytest.fixture(scope="module")

@@ -21,6 +21,10 @@ ncu256)
 ncufull16)
   DRT_BENCH_SKIP_BASELINES=1 DRT_BENCH_SPP=16 timeout 600 python bench.py --steps 1 --warmup 3 > gpurun_out/plain16.log 2>&1 &&
   DRT_BENCH_SKIP_BASELINES=1 DRT_BENCH_SPP=16 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_render -c 1 -o gpurun_out/render_full -f python bench.py --steps 1 --warmup 3 > gpurun_out/ncu_full.log 2>&1 ;;
+ncurg)
+  # the regrouping kernel (variant 16), full set on a 16-spp launch
+  DRT_VARIANT=16 DRT_BENCH_SKIP_BASELINES=1 DRT_BENCH_SPP=16 timeout 600 python bench.py --steps 1 --warmup 3 > gpurun_out/plain_rg.log 2>&1 &&
+  DRT_VARIANT=16 DRT_BENCH_SKIP_BASELINES=1 DRT_BENCH_SPP=16 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_render_regroup -c 1 -o gpurun_out/render_rg -f python bench.py --steps 1 --warmup 3 > gpurun_out/ncu_rg.log 2>&1 ;;
 sweep)
   timeout 900 python tools/sweep.py $SWEEP_ARGS > gpurun_out/sweep.jsonl 2> gpurun_out/sweep.err ;;
 *)

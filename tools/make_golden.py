@@ -32,6 +32,7 @@ SCENE_CASES = {
     "mc_transparency_test": (160, 90, 96, 54, 4, True, 2),
     "bvhsplit_test": (160, 90, 96, 54, 2, True, 2),
     "cube": (96, 54, 64, 36, 2, True, 2),
+    "sunshadow_test": (160, 90, 96, 54, 4, True, 2),      # the reference's models/test/sunshadowTest.glb UNCHANGED: its albedo is a JPEG (stb decode path)
 }
 
 
@@ -151,9 +152,12 @@ def make_scene(R, name, case):
 
 def main():
     R = O.RefOracle()
-    make_kat(R)
+    only = sys.argv[1:]  # scene names: regenerate just these (the KATs stay as they are)
+    if not only:
+        make_kat(R)
     for name, case in SCENE_CASES.items():
-        make_scene(R, name, case)
+        if not only or name in only:
+            make_scene(R, name, case)
 
 
 if __name__ == "__main__":
