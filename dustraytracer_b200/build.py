@@ -25,6 +25,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-Xcompiler", "-fPIC,-fno-fast-math,-ffp-contract=off",
 ]
+NVCC_FLAGS += os.environ.get("DRT_NVCC_EXTRA", "").split()  # measurement builds only (e.g. -DDRT_RG_CTX=384)
 CUDA_SOURCES = ["drt_kernels.cu", "drt_api.cu"]
 HOST_SOURCES = ["drt_gltf.cpp", "drt_gltf_robust.cpp", "drt_png.cpp", "drt_jpeg.cpp"]
 

@@ -69,8 +69,9 @@ __device__ __forceinline__ void flush_counters(Counters* c, const PathCounters& 
 	}
 }
 
+// VARIANT 17 / 18 = variant 4 / 15 with the first DRT_SSTACK entries of the traversal stack in shared memory (SharedLaneStack).
 template <bool STRICT, bool STATS, int VARIANT>
-__global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : ((VARIANT == 8 || VARIANT == 15) ? 6 : (VARIANT >= 4 ? VARIANT + 2 : 1))) k_render(const __grid_constant__ RenderParams P, const bool rtl, const int warps_per_block,
+__global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : ((VARIANT == 8 || VARIANT >= 15) ? 6 : (VARIANT >= 4 ? VARIANT + 2 : 1))) k_render(const __grid_constant__ RenderParams P, const bool rtl, const int warps_per_block,
 	const PhasedTuning tune)
 {
 	int x, y;
@@ -87,6 +88,11 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 		V3 acc = mk3(0.f, 0.f, 0.f);
 		if (valid) { const float4 a4 = P.accum[p]; acc = mk3(a4.x, a4.y, a4.z); }
 		__shared__ alignas(16) uint8_t lut[DRT_PERMUTE_LUT_BYTES];
+		if (VARIANT == 17 || VARIANT == 18) {
+			__shared__ uint32_t stack_words[DRT_SSTACK_WORDS];
+			acc = render_warp_phased<STRICT, STATS, NODE_FMT_F32, VARIANT == 18, SharedLaneStack>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st, lut, stack_words);
+		}
+		else
 		acc = render_warp_phased<STRICT, STATS, (VARIANT == 3 || VARIANT == 7 || VARIANT == 8) ? NODE_FMT_Q8 : NODE_FMT_F32, VARIANT == 15>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st, lut);
 		if (valid) {
 			P.accum[p] = make_float4(acc.x, acc.y, acc.z, 0.f);
@@ -538,10 +544,14 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 		}
 	}
 	if (cfg.auto_variant && variant == 4 && P.scene.num_tris >= DRT_TRI2_MIN_TRIS) variant = 15;
+	if ((variant == 17 || variant == 18) && (P.scene.nodes_f32 == nullptr || threads != 128)) variant = variant == 17 ? 4 : 15; // (shared-memory stack: fp32 nodes, 128 threads)
 	if (variant == 15 && (P.scene.nodes_f32 == nullptr || threads > 128)) variant = 4; // (two-triangle TRI step: fp32 nodes, 128 threads)
 	if ((variant == 2 || (variant >= 4 && variant <= 6)) && P.scene.nodes_f32 == nullptr) variant = threads <= 128 ? 7 : 3;
 	if (variant >= 7 && threads > 128) variant = 3;
 	if (variant >= 4 && variant <= 6 && threads > 128) variant = 2;
+	if (variant == 17) k_render<STRICT, STATS, 17><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+	else if (variant == 18) k_render<STRICT, STATS, 18><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+	else
 	if (variant == 7) k_render<STRICT, STATS, 7><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else if (variant == 8) k_render<STRICT, STATS, 8><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else if (variant == 15) k_render<STRICT, STATS, 15><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);

@@ -135,6 +135,29 @@ struct LaneStack {
 	DRT_HD void get(int i, uint32_t& vx, uint32_t& vy) const { vx = x[i]; vy = y[i]; }
 };
 
+// The same stack with its first DRT_SSTACK entries in SHARED memory ([entry][thread] words, conflict-free) and only the rest in
+// local memory: measured depths are <= 3 (room.glb) ... 7 (soup-10M), so the local part is never touched on the bundled scenes.
+// ncu on the all-local stack: 22-30 % of the kernel's L1 sector traffic was local loads / stores (profiles/r02a_*).
+#ifndef DRT_SSTACK
+#define DRT_SSTACK 8
+#endif
+#define DRT_SSTACK_THREADS 128
+#define DRT_SSTACK_WORDS (2 * DRT_SSTACK * DRT_SSTACK_THREADS)
+struct SharedLaneStack {
+	uint32_t* s; // shared-memory words of this thread: s[(2 * i) * DRT_SSTACK_THREADS], s[(2 * i + 1) * DRT_SSTACK_THREADS]
+	uint32_t lx[DRT_PSTACK - DRT_SSTACK], ly[DRT_PSTACK - DRT_SSTACK];
+	DRT_HD void put(int i, uint32_t vx, uint32_t vy)
+	{
+		if (i < DRT_SSTACK) { s[(2 * i) * DRT_SSTACK_THREADS] = vx; s[(2 * i + 1) * DRT_SSTACK_THREADS] = vy; }
+		else { lx[i - DRT_SSTACK] = vx; ly[i - DRT_SSTACK] = vy; }
+	}
+	DRT_HD void get(int i, uint32_t& vx, uint32_t& vy) const
+	{
+		if (i < DRT_SSTACK) { vx = s[(2 * i) * DRT_SSTACK_THREADS]; vy = s[(2 * i + 1) * DRT_SSTACK_THREADS]; }
+		else { vx = lx[i - DRT_SSTACK]; vy = ly[i - DRT_SSTACK]; }
+	}
+};
+
 DRT_HD void trav_begin(LaneTrav& L, float tmax)
 {
 	L.ng_base = 0u; L.ng_bits = 0x80000000u; // root: one pending inner slot, imask 0 -> relative index 0
@@ -610,15 +633,19 @@ __device__ __forceinline__ void permute_lut_store(uint8_t* lut, uint4 v)
 	__syncthreads();
 }
 
+__device__ __forceinline__ void stack_bind(LaneStack&, uint32_t*) {}
+__device__ __forceinline__ void stack_bind(SharedLaneStack& K, uint32_t* words) { K.s = words + threadIdx.x; }
+
 // One warp: every lane owns one pixel (valid or not) for all samples of the launch.
-template <bool STRICT, bool STATS, int FMT, bool TRI2 = false>
+template <bool STRICT, bool STATS, int FMT, bool TRI2 = false, class STACK = LaneStack>
 __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const PhasedTuning T, uint32_t x, uint32_t y, bool valid,
-	bool rtl, V3 acc, PathCounters& pc, TraceStats* st, uint8_t* lut)
+	bool rtl, V3 acc, PathCounters& pc, TraceStats* st, uint8_t* lut, uint32_t* stack_words = nullptr)
 {
 	const uint4 lut_part = permute_lut_load();
 	LanePath S;
 	LaneTrav L;
-	LaneStack K;
+	STACK K;
+	stack_bind(K, stack_words);
 	RayBox R;
 	S.acc = acc; S.k = 0; S.fn = mk3(0.f, 0.f, 0.f);
 	S.o = mk3(0.f, 0.f, 0.f); S.d = mk3(0.f, 0.f, 1.f);

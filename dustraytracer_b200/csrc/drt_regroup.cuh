@@ -54,7 +54,8 @@ enum {
 };
 enum { RFL_SHADOW = 1, RFL_FLIP = 2, RFL_SKY = 4, RFL_NEWPIX = 8 };
 
-#define DRT_RG_QCAP (2 * DRT_RG_CTX) // ring capacity per queue (power of two): a context holds its old slot until the round ends
+// ring capacity per queue: a power of two >= 2 * DRT_RG_CTX (a context holds its old slot until the round ends)
+#define DRT_RG_QCAP (DRT_RG_CTX <= 128 ? 256 : (DRT_RG_CTX <= 256 ? 512 : (DRT_RG_CTX <= 512 ? 1024 : 2048)))
 #define DRT_RG_STATE_BYTES ((size_t)RF_COUNT * DRT_RG_CTX * 4)
 #define DRT_RG_QUEUE_BYTES ((size_t)RQ_COUNT * DRT_RG_QCAP * 2)
 #define DRT_RG_SMEM_BYTES (DRT_RG_STATE_BYTES + DRT_RG_QUEUE_BYTES)

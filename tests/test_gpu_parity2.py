@@ -270,3 +270,39 @@ def test_production_mode_has_no_bias_floor(drt, name, sun, bounces):
     assert rmse[64] <= 0.02
     assert 0.125 * 0.75 <= ratio <= 0.125 * 1.25
     assert abs(bias[4096]) <= 1e-3
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the regrouping arm (variant 16, drt_regroup.cuh)
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,size", [("room", (101, 67)), ("animemaid", (37, 5)), ("cornell_box", (8, 4)), ("dense_monkey", (250, 131))])
+def test_regrouping_kernel_matches_the_megakernel(drt, name, size):
+    """Block-level regrouping (contexts in shared memory, five step queues, pixels from a global counter) against the per-warp
+    voting kernel: ragged image sizes, several launches of 1..5 samples. STRICT arithmetic: the same bits and ray counts.
+    Production arithmetic: nvcc contracts multiply-adds differently in the two code shapes, so a few paths diverge; the images
+    must agree like two renders of the same estimator (tiny RMSE, no bias) and the ray counts within 0.5 %."""
+    scene = gpu_scene(drt, name)
+    cam = drt.Camera()
+    st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=4, max_samples=100000)
+
+    def run(variant, batches, flags):
+        r = drt.Renderer(flags=flags)
+        r.set_tuning(variant, 0)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(*size)
+        for b in batches:
+            r.Render(cam, scene, b)
+        return r.readback(drt.DRT_ACCUM_RGB32F), r.readback(drt.DRT_RGBA32F), r.counters()
+
+    for batches in ([1, 1, 1, 1, 1], [3, 2], [5]):
+        a4, d4, c4 = run(4, batches, STRICT)
+        a, d, c = run(16, batches, STRICT)
+        assert np.array_equal(bits(a), bits(a4)) and np.array_equal(bits(d), bits(d4)), batches
+        assert c == c4, batches
+    a4, _, c4 = run(4, [64], 0)
+    a, _, c = run(16, [64], 0)
+    diff = (a.astype(np.float64) - a4) / 64
+    rays4, rays = c4["closest_rays"] + c4["shadow_rays"], c["closest_rays"] + c["shadow_rays"]
+    print("%s production mode, variant 16 vs 4 at 64 spp: RMSE %.2e, mean %+.1e, rays %d vs %d" % (name, np.sqrt((diff ** 2).mean()), diff.mean(), rays, rays4))
+    assert np.sqrt((diff ** 2).mean()) <= 0.02 and abs(diff.mean()) <= 2e-3
+    assert abs(rays - rays4) <= 0.005 * rays4 + 8
