@@ -104,6 +104,19 @@ SIGNATURES = {
     "drt_renderer_resolve": (_i, [_vp, _u]),
     "drt_renderer_get_counters": (_i, [_vp, _P(drt_counters), _i]),
     "drt_trace_primary": (_i, [_vp, _P(drt_camera), _vp, _u, _vp, _sz]),
+    "drt_multi_create": (_i, [_vp, ctypes.c_int32, _P(_vp)]),
+    "drt_multi_destroy": (None, [_vp]),
+    "drt_multi_device_count": (_i, [_vp]),
+    "drt_multi_set_scene": (_i, [_vp, _vp, _vp]),
+    "drt_multi_set_sharding": (_i, [_vp, ctypes.c_int32]),
+    "drt_multi_set_flags": (_i, [_vp, _u]),
+    "drt_multi_resize": (_i, [_vp, _u, _u]),
+    "drt_multi_render": (_i, [_vp, _P(drt_camera), _P(drt_settings), _u, _P(ctypes.c_float)]),
+    "drt_multi_reset": (_i, [_vp]),
+    "drt_multi_sample_count": (_u, [_vp]),
+    "drt_multi_readback": (_i, [_vp, _i, _vp, _sz]),
+    "drt_multi_get_counters": (_i, [_vp, _P(drt_counters), _i]),
+    "drt_multi_nccl_reduces": (_i, [_vp]),
     "drt_trace_rays": (_i, [_vp, _vp, _vp, _vp, _sz, _i, _vp]),
     "drt_trace_primary_noalloc": (_i, [_vp, _P(drt_camera), _vp, _u, _vp, _sz]),
     "drt_default_camera": (None, [_P(drt_camera)]),

@@ -323,6 +323,67 @@ class Renderer:
             pass
 
 
+class MultiRenderer:
+    """N GPUs of one node behind one handle (drt_multi_*): replicated scene, sample-range or image-tile sharding, one NCCL
+    reduce of the accumulation buffers per render call, all inside libdrt.so (no torch.distributed)."""
+
+    def __init__(self, devices, flags=0):
+        self._h = ctypes.c_void_p()
+        arr = (ctypes.c_int32 * len(devices))(*devices)
+        check(_lib.lib().drt_multi_create(arr, len(devices), ctypes.byref(self._h)))
+        self.devices = list(devices)
+        self.m_RendererSettings = RendererSettings()
+        if flags:
+            self.set_flags(flags)
+
+    def set_flags(self, flags):
+        check(_lib.lib().drt_multi_set_flags(self._h, flags))
+
+    def set_scene(self, scene):
+        check(_lib.lib().drt_multi_set_scene(self._h, scene._h, None))
+
+    def set_sharding(self, tiles=False):
+        check(_lib.lib().drt_multi_set_sharding(self._h, 1 if tiles else 0))
+
+    def ResizeBuffer(self, width, height):
+        check(_lib.lib().drt_multi_resize(self._h, width, height))
+        self._size = (width, height)
+
+    def Render(self, cam, n_samples=1):
+        ms = ctypes.c_float()
+        check(_lib.lib().drt_multi_render(self._h, ctypes.byref(cam), ctypes.byref(self.m_RendererSettings), n_samples, ctypes.byref(ms)))
+        return ms.value
+
+    def resetAccumulationBuffer(self):
+        check(_lib.lib().drt_multi_reset(self._h))
+
+    def getSampleCount(self):
+        return _lib.lib().drt_multi_sample_count(self._h)
+
+    def nccl_reduces(self):
+        return _lib.lib().drt_multi_nccl_reduces(self._h)
+
+    def readback(self, fmt=DRT_RGBA32F):
+        w, h = self._size
+        shape, dt = {DRT_RGBA32F: ((h, w, 4), np.float32), DRT_RGBA8: ((h, w, 4), np.uint8), DRT_ACCUM_RGB32F: ((h, w, 3), np.float32)}[fmt]
+        out = np.empty(shape, dt)
+        check(_lib.lib().drt_multi_readback(self._h, fmt, out.ctypes.data, out.nbytes))
+        return out
+
+    def counters(self, reset=False):
+        c = drt_counters()
+        check(_lib.lib().drt_multi_get_counters(self._h, ctypes.byref(c), 1 if reset else 0))
+        return {k: getattr(c, k) for k, _ in drt_counters._fields_}
+
+    def __del__(self):
+        try:
+            if self._h:
+                _lib.lib().drt_multi_destroy(self._h)
+                self._h = ctypes.c_void_p()
+        except Exception:
+            pass
+
+
 def tile_owner_mask(width, height, first_tile, stride):
     """Boolean (height, width) mask of the pixels a renderer with set_tile_schedule(first_tile, stride) renders: the 8x4
     tiles whose row-major index t satisfies t >= first_tile and (t - first_tile) % stride == 0 (drt_kernels.cu pixel_of_thread)."""

@@ -790,10 +790,12 @@ static LaunchConfig launch_config(const drt_renderer* r)
 	return cfg;
 }
 
-extern "C" int drt_renderer_render(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, const drt_settings* settings,
-	uint32_t n_samples, float* ms_or_null)
+// Launch half of drt_renderer_render: enqueues the batch on the renderer's stream and returns without waiting.
+// *launched = samples the launch renders (0: nothing was enqueued), candidate / probing = the auto-tuner's bookkeeping.
+static int render_launch(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, const drt_settings* settings, uint32_t n_samples,
+	uint32_t* launched, int* candidate_out, bool* probing_out)
 {
-	if (ms_or_null) *ms_or_null = 0.f;
+	*launched = 0; *candidate_out = -1; *probing_out = false;
 	RenderParams P;
 	int rc = make_render_params(r, cam, scene, settings, P);
 	if (rc) return rc;
@@ -812,6 +814,7 @@ extern "C" int drt_renderer_render(drt_renderer* r, const drt_camera* cam, const
 		if (n > room) n = (uint32_t)room;
 	}
 	if (n == 0) return DRT_OK;
+	*launched = n;
 	P.frame_first = (uint32_t)next_frame;
 	P.frame_stride = r->stride;
 	P.n_samples = n;
@@ -827,13 +830,26 @@ extern "C" int drt_renderer_render(drt_renderer* r, const drt_camera* cam, const
 	DRT_CUDA(cudaEventRecord(r->ev0, r->stream));
 	DRT_CUDA(launch_render(P, cfg, r->stream, &r->kernel_launches));
 	DRT_CUDA(cudaEventRecord(r->ev1, r->stream));
+	*candidate_out = candidate; *probing_out = probing;
+	r->samples_done += n;
+	r->frame_index += n;
+	return DRT_OK;
+}
+
+extern "C" int drt_renderer_render(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, const drt_settings* settings,
+	uint32_t n_samples, float* ms_or_null)
+{
+	if (ms_or_null) *ms_or_null = 0.f;
+	uint32_t n = 0;
+	int candidate = -1;
+	bool probing = false;
+	const int rc = render_launch(r, cam, scene, settings, n_samples, &n, &candidate, &probing);
+	if (rc || n == 0) return rc;
 	DRT_CUDA(cudaEventSynchronize(r->ev1)); // like Renderer.cu:105-106 the call returns with the frame done
 	float ms = 0.f;
 	if (ms_or_null || candidate >= 0) DRT_CUDA(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
 	if (ms_or_null) *ms_or_null = ms;
 	if (candidate >= 0) autotune_record(r, candidate, probing, ms);
-	r->samples_done += n;
-	r->frame_index += n;
 	return DRT_OK;
 }
 
@@ -943,6 +959,270 @@ extern "C" int drt_trace_rays(drt_renderer* r, const drt_scene* scene, const flo
 	r->kernel_launches++;
 	DRT_CUDA(cudaMemcpyAsync(out_host, d_h.p, n_rays * sizeof(Hit), cudaMemcpyDeviceToHost, r->stream));
 	DRT_CUDA(cudaStreamSynchronize(r->stream));
+	return DRT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// multi-device renderer: N GPUs of one node behind ONE handle, NCCL inside the library
+// ---------------------------------------------------------------------------------------------
+// One host thread drives all devices: every device gets a replica of the scene (built there) and a renderer; a render call
+// enqueues each device's share on that device's stream (sample-range sharding: device g renders frame indices g+1, g+1+N, ...;
+// or image-tile sharding: device g renders the 8x4 tiles g, g+N, ... of every frame), then ONE ncclReduce(sum) of the W*H float4
+// accumulation buffers into a total buffer on the root device, then the root's resolve kernel (display = total / samples).
+// NCCL is bound at run time (dlopen of libnccl.so.2: the library has no link-time dependency on it and loads on hosts without it).
+#include <dlfcn.h>
+#include <nccl.h>
+
+namespace {
+
+struct NcclApi {
+	void* handle = nullptr;
+	ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+	ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+	ncclResult_t (*GroupStart)() = nullptr;
+	ncclResult_t (*GroupEnd)() = nullptr;
+	ncclResult_t (*Reduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+	const char* (*GetErrorString)(ncclResult_t) = nullptr;
+	std::string error;
+};
+
+NcclApi& nccl_api()
+{
+	static NcclApi api;
+	static std::once_flag once;
+	std::call_once(once, [] {
+		for (const char* name : { "libnccl.so.2", "libnccl.so" }) {
+			api.handle = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+			if (api.handle) break;
+		}
+		if (!api.handle) { api.error = std::string("cannot load libnccl.so.2: ") + (dlerror() ? dlerror() : "?"); return; }
+		api.CommInitAll = (decltype(api.CommInitAll))dlsym(api.handle, "ncclCommInitAll");
+		api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.handle, "ncclCommDestroy");
+		api.GroupStart = (decltype(api.GroupStart))dlsym(api.handle, "ncclGroupStart");
+		api.GroupEnd = (decltype(api.GroupEnd))dlsym(api.handle, "ncclGroupEnd");
+		api.Reduce = (decltype(api.Reduce))dlsym(api.handle, "ncclReduce");
+		api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.handle, "ncclGetErrorString");
+		if (!api.CommInitAll || !api.CommDestroy || !api.GroupStart || !api.GroupEnd || !api.Reduce) api.error = "libnccl.so.2 lacks the collective entry points";
+	});
+	return api;
+}
+
+} // namespace
+
+struct drt_multi {
+	std::vector<int> devices;
+	std::vector<drt_renderer*> r;
+	std::vector<drt_scene*> scenes;    // replicas owned by this object, one per device
+	std::vector<ncclComm_t> comms;
+	DevBuf<drt_f4> total;              // root device: sum over the devices of the accumulation buffers
+	int sharding = 0;                  // 0 = sample ranges, 1 = image tiles
+	uint32_t samples_total = 0;        // samples per pixel the total buffer holds
+	uint32_t width = 0, height = 0;
+	int nccl_reduces = 0;
+};
+
+#define DRT_NCCL(expr)                                                                                           \
+	do {                                                                                                         \
+		ncclResult_t e__ = (expr);                                                                               \
+		if (e__ != ncclSuccess) {                                                                                \
+			NcclApi& a__ = nccl_api();                                                                           \
+			return fail(DRT_ERR_CUDA, std::string(#expr) + ": " + (a__.GetErrorString ? a__.GetErrorString(e__) : "NCCL error")); \
+		}                                                                                                        \
+	} while (0)
+
+extern "C" void drt_multi_destroy(drt_multi* m)
+{
+	if (!m) return;
+	NcclApi& api = nccl_api();
+	for (size_t g = 0; g < m->comms.size() && g < m->r.size(); g++)
+		if (m->comms[g] && api.CommDestroy) { cudaSetDevice(m->devices[g]); api.CommDestroy(m->comms[g]); }
+	const int root = m->r.empty() ? -1 : m->r[0]->device; // (a handle whose creation failed may name devices that do not exist)
+	if (root >= 0) { cudaSetDevice(root); m->total.release(); }
+	for (drt_renderer* r : m->r) drt_renderer_destroy(r);
+	for (drt_scene* s : m->scenes) drt_scene_destroy(s);
+	if (root >= 0) cudaSetDevice(root);
+	delete m;
+}
+
+extern "C" int drt_multi_create(const int32_t* devices, int32_t n, drt_multi** out)
+{
+	if (!out || !devices || n < 1 || n > 64) return fail(DRT_ERR_INVALID, "drt_multi_create: need 1..64 device ordinals");
+	*out = nullptr;
+	for (int i = 0; i < n; i++) for (int j = 0; j < i; j++) if (devices[i] == devices[j]) return fail(DRT_ERR_INVALID, "drt_multi_create: a device is named twice");
+	drt_multi* m = new drt_multi();
+	m->devices.assign(devices, devices + n);
+	for (int g = 0; g < n; g++) {
+		drt_renderer* r = nullptr;
+		const int rc = drt_renderer_create(devices[g], &r);
+		if (rc) { drt_multi_destroy(m); return rc; }
+		m->r.push_back(r);
+	}
+	if (n > 1) {
+		NcclApi& api = nccl_api();
+		if (!api.error.empty()) { const std::string e = api.error; drt_multi_destroy(m); return fail(DRT_ERR_CUDA, "drt_multi_create: " + e); }
+		m->comms.assign(n, nullptr);
+		const ncclResult_t e = api.CommInitAll(m->comms.data(), n, m->devices.data());
+		if (e != ncclSuccess) {
+			const std::string msg = api.GetErrorString ? api.GetErrorString(e) : "NCCL error";
+			m->comms.clear();
+			drt_multi_destroy(m);
+			return fail(DRT_ERR_CUDA, "drt_multi_create: ncclCommInitAll: " + msg);
+		}
+	}
+	drt_multi_set_sharding(m, 0);
+	*out = m;
+	return DRT_OK;
+}
+
+extern "C" int drt_multi_device_count(const drt_multi* m) { return m ? (int)m->devices.size() : 0; }
+extern "C" int drt_multi_nccl_reduces(const drt_multi* m) { return m ? m->nccl_reduces : 0; }
+extern "C" uint32_t drt_multi_sample_count(const drt_multi* m) { return m ? m->samples_total + 1 : 0; }
+
+extern "C" int drt_multi_set_sharding(drt_multi* m, int32_t mode)
+{
+	if (!m || (mode != 0 && mode != 1)) return fail(DRT_ERR_INVALID, "drt_multi_set_sharding: mode is 0 (sample ranges) or 1 (image tiles)");
+	const uint32_t n = (uint32_t)m->devices.size();
+	m->sharding = mode;
+	for (uint32_t g = 0; g < n; g++) {
+		int rc = mode == 0 ? drt_renderer_set_tile_schedule(m->r[g], 0, 1) : drt_renderer_set_frame_schedule(m->r[g], 1, 1);
+		if (!rc) rc = mode == 0 ? drt_renderer_set_frame_schedule(m->r[g], g + 1, n) : drt_renderer_set_tile_schedule(m->r[g], g, n);
+		if (rc) return rc;
+	}
+	m->samples_total = 0;
+	return DRT_OK;
+}
+
+extern "C" int drt_multi_set_flags(drt_multi* m, uint32_t flags)
+{
+	if (!m) return fail(DRT_ERR_INVALID, "drt_multi_set_flags: null handle");
+	for (drt_renderer* r : m->r) drt_renderer_set_flags(r, flags);
+	return DRT_OK;
+}
+
+extern "C" int drt_multi_set_scene(drt_multi* m, const drt_scene* scene, const drt_bvh_params* params_or_null)
+{
+	if (!m || !scene) return fail(DRT_ERR_INVALID, "drt_multi_set_scene: null argument");
+	for (drt_scene* s : m->scenes) drt_scene_destroy(s);
+	m->scenes.clear();
+	for (size_t g = 0; g < m->devices.size(); g++) {
+		drt_scene* copy = new drt_scene();
+		copy->host = scene->host; // the host-side soup, materials and texels; the tree is built on the device it is rendered on
+		fill_stats(copy);
+		copy->stats.load_ms = scene->stats.load_ms;
+		m->scenes.push_back(copy);
+		const int rc = drt_scene_build_bvh(copy, params_or_null, m->devices[g]);
+		if (rc) return rc;
+	}
+	return drt_multi_reset(m);
+}
+
+extern "C" int drt_multi_resize(drt_multi* m, uint32_t width, uint32_t height)
+{
+	if (!m) return fail(DRT_ERR_INVALID, "drt_multi_resize: null handle");
+	for (drt_renderer* r : m->r) { const int rc = drt_renderer_resize(r, width, height); if (rc) return rc; }
+	DRT_CUDA(cudaSetDevice(m->devices[0]));
+	if (m->devices.size() > 1) DRT_CUDA(m->total.alloc((size_t)width * height));
+	m->width = width; m->height = height;
+	return drt_multi_reset(m);
+}
+
+extern "C" int drt_multi_reset(drt_multi* m)
+{
+	if (!m) return fail(DRT_ERR_INVALID, "drt_multi_reset: null handle");
+	for (drt_renderer* r : m->r) { const int rc = drt_renderer_reset(r); if (rc) return rc; }
+	m->samples_total = 0;
+	return DRT_OK;
+}
+
+extern "C" int drt_multi_render(drt_multi* m, const drt_camera* cam, const drt_settings* settings, uint32_t n_samples, float* ms_or_null)
+{
+	if (ms_or_null) *ms_or_null = 0.f;
+	if (!m || !cam) return fail(DRT_ERR_INVALID, "drt_multi_render: null argument");
+	const size_t n = m->devices.size();
+	if (m->scenes.size() != n) return fail(DRT_ERR_INVALID, "drt_multi_render: call drt_multi_set_scene first");
+	if (!m->width) return fail(DRT_ERR_INVALID, "drt_multi_render: call drt_multi_resize first");
+	if (n == 1) { // one device: exactly the single-device renderer
+		const uint32_t before = m->r[0]->samples_done;
+		const int rc = drt_renderer_render(m->r[0], cam, m->scenes[0], settings, n_samples, ms_or_null);
+		m->samples_total += m->r[0]->samples_done - before;
+		return rc;
+	}
+	drt_settings dflt;
+	if (!settings) { default_settings(&dflt); settings = &dflt; }
+	// Renderer.cu:82 for the whole frame: never more than max_samples - 1 samples in total
+	uint64_t want = n_samples;
+	const int64_t room = (int64_t)settings->max_samples - 1 - (int64_t)m->samples_total;
+	if (room <= 0) return DRT_OK;
+	if (want > (uint64_t)room) want = (uint64_t)room;
+	drt_settings per = *settings;
+	per.max_samples = 0x7fffffff; // the split below already honours the limit
+	const auto t0 = std::chrono::steady_clock::now();
+	uint32_t launched_total = 0;
+	std::vector<uint32_t> launched(n, 0);
+	for (size_t g = 0; g < n; g++) {
+		// sample ranges: device g takes every n-th sample of the batch (the first `want % n` devices one more); tiles: every device all samples
+		const uint32_t share = m->sharding == 0 ? (uint32_t)(want / n + (g < want % n ? 1 : 0)) : (uint32_t)want;
+		if (share == 0) continue;
+		int candidate = -1;
+		bool probing = false;
+		const int rc = render_launch(m->r[g], cam, m->scenes[g], &per, share, &launched[g], &candidate, &probing);
+		if (rc) return rc;
+		launched_total += m->sharding == 0 ? launched[g] : (g == 0 ? launched[g] : 0);
+	}
+	m->samples_total += launched_total;
+	// ONE reduce of the accumulation buffers to the root, enqueued behind each device's kernel on that device's stream
+	NcclApi& api = nccl_api();
+	const size_t count = (size_t)m->width * m->height * 4;
+	DRT_NCCL(api.GroupStart());
+	for (size_t g = 0; g < n; g++) {
+		const ncclResult_t e = api.Reduce(fb_accum(m->r[g]), g == 0 ? (void*)m->total.p : nullptr, count, ncclFloat, ncclSum, 0, m->comms[g], m->r[g]->stream);
+		if (e != ncclSuccess) { api.GroupEnd(); return fail(DRT_ERR_CUDA, std::string("ncclReduce: ") + (api.GetErrorString ? api.GetErrorString(e) : "NCCL error")); }
+	}
+	DRT_NCCL(api.GroupEnd());
+	m->nccl_reduces++;
+	DRT_CUDA(cudaSetDevice(m->devices[0]));
+	if (m->samples_total > 0) {
+		DRT_CUDA(launch_resolve(fb_display(m->r[0]), m->total.p, (int)((size_t)m->width * m->height), (float)m->samples_total, m->r[0]->stream));
+		m->r[0]->kernel_launches++;
+	}
+	for (size_t g = 0; g < n; g++) {
+		DRT_CUDA(cudaSetDevice(m->devices[g]));
+		DRT_CUDA(cudaStreamSynchronize(m->r[g]->stream));
+	}
+	DRT_CUDA(cudaSetDevice(m->devices[0]));
+	if (ms_or_null) *ms_or_null = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+	return DRT_OK;
+}
+
+extern "C" int drt_multi_readback(drt_multi* m, drt_format format, void* host, size_t bytes)
+{
+	if (!m || !host || !m->width) return fail(DRT_ERR_INVALID, "drt_multi_readback: bad argument");
+	drt_renderer* r0 = m->r[0];
+	if (m->devices.size() == 1 || format != DRT_ACCUM_RGB32F) return drt_renderer_readback(r0, format, host, bytes); // display lives on the root
+	// accumulation sums of the whole frame = the reduced total
+	if (renderer_bind(r0)) return DRT_ERR_CUDA;
+	const size_t np = (size_t)m->width * m->height;
+	if (bytes < np * 12) return fail(DRT_ERR_INVALID, "drt_multi_readback: buffer too small");
+	if (r0->staging.n < np * 12) DRT_CUDA(r0->staging.alloc(np * 12));
+	DRT_CUDA(launch_pack_rgb32f((float*)r0->staging.p, m->total.p, (int)np, r0->stream));
+	r0->kernel_launches++;
+	DRT_CUDA(cudaMemcpyAsync(host, r0->staging.p, np * 12, cudaMemcpyDeviceToHost, r0->stream));
+	DRT_CUDA(cudaStreamSynchronize(r0->stream));
+	return DRT_OK;
+}
+
+extern "C" int drt_multi_get_counters(drt_multi* m, drt_counters* out, int reset)
+{
+	if (!m || !out) return fail(DRT_ERR_INVALID, "drt_multi_get_counters: null argument");
+	memset(out, 0, sizeof(*out));
+	for (drt_renderer* r : m->r) {
+		drt_counters c;
+		const int rc = drt_renderer_get_counters(r, &c, reset);
+		if (rc) return rc;
+		out->closest_rays += c.closest_rays; out->shadow_rays += c.shadow_rays; out->node_visits += c.node_visits; out->tri_tests += c.tri_tests;
+		out->tie_events += c.tie_events; out->alpha_tests += c.alpha_tests; out->texel_clamps += c.texel_clamps;
+		if (c.max_stack > out->max_stack) out->max_stack = c.max_stack;
+	}
 	return DRT_OK;
 }
 

@@ -207,6 +207,29 @@ int drt_renderer_get_counters(drt_renderer* r, drt_counters* out, int reset);
 int drt_trace_primary(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, uint32_t frame_index,
 	drt_hit* out_host, size_t count);
 
+/* ---- N GPUs of one node behind one handle, NCCL inside the library (drt_renderer_create(device_ordinals[], n); 8e) ----
+ * What the reference's only kind of caller -- a C++ host, Editor/EditorLayer.cpp:317-318 -- needs to use more than one GPU
+ * without Python: every device gets a replica of the scene (built there) and a renderer; drt_multi_render splits a batch of
+ * samples over the devices (mode 0, default: device g renders frame indices g+1, g+1+N, ...; mode 1: device g renders the 8x4
+ * tiles g, g+N, ... of every frame, which reproduces the one-GPU bits), runs ONE ncclReduce(sum) over NVLink of the W*H float4
+ * accumulation buffers to the first device and resolves the display buffer there. n = 1 is exactly the single-device renderer.
+ * One host thread drives all devices (ncclCommInitAll); NCCL is loaded at run time (libnccl.so.2), so the library has no
+ * link-time dependency on it and drt_multi_create fails with a message where it is missing. */
+typedef struct drt_multi drt_multi;
+int drt_multi_create(const int32_t* device_ordinals, int32_t n, drt_multi** out);
+void drt_multi_destroy(drt_multi* m);
+int drt_multi_device_count(const drt_multi* m);
+int drt_multi_set_scene(drt_multi* m, const drt_scene* scene, const drt_bvh_params* params_or_null); /* replicates + builds on every device */
+int drt_multi_set_sharding(drt_multi* m, int32_t mode); /* 0 = sample ranges, 1 = image tiles; resets the accumulation */
+int drt_multi_set_flags(drt_multi* m, uint32_t flags);
+int drt_multi_resize(drt_multi* m, uint32_t width, uint32_t height);
+int drt_multi_render(drt_multi* m, const drt_camera* cam, const drt_settings* settings, uint32_t n_samples, float* ms_or_null);
+int drt_multi_reset(drt_multi* m);
+uint32_t drt_multi_sample_count(const drt_multi* m); /* samples in the frame + 1, like Renderer::getSampleCount */
+int drt_multi_readback(drt_multi* m, drt_format format, void* host, size_t bytes);
+int drt_multi_get_counters(drt_multi* m, drt_counters* out, int reset); /* summed over the devices */
+int drt_multi_nccl_reduces(const drt_multi* m); /* collectives issued so far */
+
 /* Ray-level parity probe: n_rays caller-given rays (origins / directions: 3 floats each, host memory; directions as the path
  * would pass them, not normalised) through the very step functions the render kernels run (wide-node slab test, Moller-Trumbore
  * in the reference's operation order, alpha cut-out). anyhit = 0: TraceRay closest hit (Kernel/TraceRay.cu:15-33 ->

@@ -133,4 +133,46 @@ private:
 	drt_renderer* h_ = nullptr;
 };
 
+// N GPUs of one node behind one object (drt_multi_*: replicated scene, sample-range or image-tile sharding, one NCCL reduce of
+// the accumulation buffers per Render call, inside the library). The methods mirror Renderer's.
+class MultiRenderer {
+public:
+	RendererSettings m_RendererSettings;
+
+	explicit MultiRenderer(const std::vector<int32_t>& devices) { check(drt_multi_create(devices.data(), (int32_t)devices.size(), &h_)); }
+	MultiRenderer(const MultiRenderer&) = delete;
+	MultiRenderer& operator=(const MultiRenderer&) = delete;
+	~MultiRenderer() { drt_multi_destroy(h_); }
+
+	void setScene(const Scene& scene) { check(drt_multi_set_scene(h_, scene.handle(), nullptr)); } // replicates and builds on every device
+	void setSharding(bool tiles) { check(drt_multi_set_sharding(h_, tiles ? 1 : 0)); }
+	void ResizeBuffer(uint32_t width, uint32_t height) { check(drt_multi_resize(h_, width, height)); w_ = width; hgt_ = height; }
+	void Render(const Camera* cam, float* delta, uint32_t n_samples = 1) { check(drt_multi_render(h_, cam, &m_RendererSettings, n_samples, delta)); }
+	void resetAccumulationBuffer() { check(drt_multi_reset(h_)); }
+	uint32_t getSampleCount() const { return drt_multi_sample_count(h_); }
+	int deviceCount() const { return drt_multi_device_count(h_); }
+	std::vector<float> readbackRGBA32F()
+	{
+		std::vector<float> px((size_t)w_ * hgt_ * 4);
+		check(drt_multi_readback(h_, DRT_RGBA32F, px.data(), px.size() * sizeof(float)));
+		return px;
+	}
+	std::vector<uint8_t> readbackRGBA8()
+	{
+		std::vector<uint8_t> px((size_t)w_ * hgt_ * 4);
+		check(drt_multi_readback(h_, DRT_RGBA8, px.data(), px.size()));
+		return px;
+	}
+	drt_counters counters(bool reset = false)
+	{
+		drt_counters c;
+		check(drt_multi_get_counters(h_, &c, reset ? 1 : 0));
+		return c;
+	}
+
+private:
+	drt_multi* h_ = nullptr;
+	uint32_t w_ = 0, hgt_ = 0;
+};
+
 } // namespace drt

@@ -63,7 +63,7 @@ static void write_png(FILE* f, uint32_t w, uint32_t h, const std::vector<uint8_t
 
 static int usage()
 {
-	fprintf(stderr, "usage: drt_render scene.glb [--width W] [--height H] [--spp N] [--bounces B] [--sun] [--batch K] [--device D]\n"
+	fprintf(stderr, "usage: drt_render scene.glb [--width W] [--height H] [--spp N] [--bounces B] [--sun] [--batch K] [--device D] [--gpus N [--tiles]]\n"
 		"                  [--pos x y z] [--dir x y z] [--robust] [--out image.ppm|image.pfm|image.png]\n");
 	return 2;
 }
@@ -73,7 +73,8 @@ int main(int argc, char** argv)
 	if (argc < 2) return usage();
 	std::string scene_path = argv[1], out;
 	uint32_t W = 1280, H = 720, spp = 64, batch = 64;
-	int device = 0;
+	int device = 0, gpus = 1;
+	bool tiles = false;
 	uint32_t load_flags = DRT_LOAD_REFERENCE_COMPAT;
 	drt::Camera cam;
 	drt::RendererSettings settings;
@@ -87,6 +88,8 @@ int main(int argc, char** argv)
 		else if (a == "--batch") { need(1); batch = (uint32_t)atoi(argv[++i]); }
 		else if (a == "--bounces") { need(1); settings.ray_bounce_limit = atoi(argv[++i]); }
 		else if (a == "--device") { need(1); device = atoi(argv[++i]); }
+		else if (a == "--gpus") { need(1); gpus = atoi(argv[++i]); }
+		else if (a == "--tiles") tiles = true;
 		else if (a == "--sun") settings.enable_sunlight = 1;
 		else if (a == "--robust") load_flags = DRT_LOAD_ROBUST;
 		else if (a == "--out") { need(1); out = argv[++i]; }
@@ -97,34 +100,66 @@ int main(int argc, char** argv)
 	try {
 		drt::Scene scene;
 		if (!scene.loadGLTFmodel(scene_path.c_str(), load_flags)) throw drt::Error(DRT_ERR_IO, drt_last_error());
-		drt::BVHBuilder builder;
-		builder.device = device;
-		builder.buildIterative(scene);
-		drt::Renderer renderer(device);
-		renderer.m_RendererSettings = settings;
-		renderer.ResizeBuffer(W, H);
 		double ms_total = 0.0;
-		for (uint32_t done = 0; done < spp;) {
-			const uint32_t n = spp - done < batch ? spp - done : batch;
-			float ms = 0.f;
-			renderer.Render(&cam, scene, &ms, n);
-			ms_total += ms;
-			done += n;
+		drt_counters c;
+		uint32_t samples = 0;
+		std::vector<float> px32;
+		std::vector<uint8_t> px8;
+		const bool pfm = out.size() > 4 && out.substr(out.size() - 4) == ".pfm";
+		if (gpus > 1) {
+			// N GPUs of this node: drt_multi (replicated scene, one NCCL reduce of the accumulation buffers per batch)
+			std::vector<int32_t> devs;
+			for (int g = 0; g < gpus; g++) devs.push_back(device + g);
+			drt::MultiRenderer renderer(devs);
+			renderer.m_RendererSettings = settings;
+			renderer.setScene(scene);
+			if (tiles) renderer.setSharding(true);
+			renderer.ResizeBuffer(W, H);
+			for (uint32_t done = 0; done < spp;) {
+				const uint32_t n = spp - done < batch ? spp - done : batch;
+				float ms = 0.f;
+				renderer.Render(&cam, &ms, n);
+				ms_total += ms;
+				done += n;
+			}
+			c = renderer.counters();
+			samples = renderer.getSampleCount() - 1;
+			if (!out.empty()) { if (pfm) px32 = renderer.readbackRGBA32F(); else px8 = renderer.readbackRGBA8(); }
+			drt::BVHBuilder builder; // (stats of one replica for the report)
+			builder.device = device;
+			builder.buildIterative(scene);
 		}
-		const drt_counters c = renderer.counters();
+		else {
+			drt::BVHBuilder builder;
+			builder.device = device;
+			builder.buildIterative(scene);
+			drt::Renderer renderer(device);
+			renderer.m_RendererSettings = settings;
+			renderer.ResizeBuffer(W, H);
+			for (uint32_t done = 0; done < spp;) {
+				const uint32_t n = spp - done < batch ? spp - done : batch;
+				float ms = 0.f;
+				renderer.Render(&cam, scene, &ms, n);
+				ms_total += ms;
+				done += n;
+			}
+			c = renderer.counters();
+			samples = renderer.getSampleCount() - 1;
+			if (!out.empty()) { if (pfm) px32 = renderer.readbackRGBA32F(); else px8 = renderer.readbackRGBA8(); }
+		}
 		const drt_scene_stats st = scene.stats();
 		const double rays = (double)(c.closest_rays + c.shadow_rays);
 		if (!out.empty()) {
 			FILE* f = fopen(out.c_str(), "wb");
 			if (!f) throw drt::Error(DRT_ERR_IO, "cannot open the output file");
-			const bool pfm = out.size() > 4 && out.substr(out.size() - 4) == ".pfm";
 			if (pfm) {
-				std::vector<float> px = renderer.readbackRGBA32F();
+				const std::vector<float>& px = px32;
 				fprintf(f, "PF\n%u %u\n-1.0\n", W, H); // PFM stores rows bottom-up, like the frame buffer
 				for (size_t p = 0; p < (size_t)W * H; p++) fwrite(&px[4 * p], sizeof(float), 3, f);
 			}
 			else {
-				std::vector<uint8_t> px = renderer.readbackRGBA8(), rgb((size_t)W * H * 3);
+				const std::vector<uint8_t>& px = px8;
+				std::vector<uint8_t> rgb((size_t)W * H * 3);
 				for (uint32_t y = 0; y < H; y++)
 					for (uint32_t x = 0; x < W; x++) memcpy(&rgb[3 * ((size_t)y * W + x)], &px[4 * ((size_t)(H - 1 - y) * W + x)], 3);
 				if (out.size() > 4 && out.substr(out.size() - 4) == ".png") write_png(f, W, H, rgb);
@@ -136,9 +171,9 @@ int main(int argc, char** argv)
 			fclose(f);
 		}
 		printf("{\"scene\": \"%s\", \"triangles\": %llu, \"wide_nodes\": %llu, \"build_ms\": %.3f, \"width\": %u, \"height\": %u, \"spp\": %u, "
-			"\"render_ms\": %.3f, \"rays\": %.0f, \"Mrays_s\": %.1f, \"samples\": %u}\n",
+			"\"render_ms\": %.3f, \"rays\": %.0f, \"Mrays_s\": %.1f, \"samples\": %u, \"gpus\": %d}\n",
 			scene_path.c_str(), (unsigned long long)st.triangles, (unsigned long long)st.wide_nodes, st.build_ms, W, H, spp, ms_total, rays,
-			ms_total > 0 ? rays / ms_total / 1e3 : 0.0, renderer.getSampleCount() - 1);
+			ms_total > 0 ? rays / ms_total / 1e3 : 0.0, samples, gpus);
 	}
 	catch (const drt::Error& e) {
 		fprintf(stderr, "drt_render: %s (status %d)\n", e.what(), e.status);
