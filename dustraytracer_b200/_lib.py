@@ -61,7 +61,7 @@ class drt_counters(ctypes.Structure):
 assert ctypes.sizeof(drt_camera) == 88 and ctypes.sizeof(drt_settings) == 64 and ctypes.sizeof(drt_material) == 44
 
 DRT_RGBA32F, DRT_RGBA8, DRT_ACCUM_RGB32F = 0, 1, 2
-DRT_FLAG_STRICT, DRT_FLAG_HOST_ARG_ORDER, DRT_FLAG_STATS, DRT_FLAG_EXTENDED_MATERIALS = 1, 2, 4, 8
+DRT_FLAG_STRICT, DRT_FLAG_HOST_ARG_ORDER, DRT_FLAG_STATS, DRT_FLAG_EXTENDED_MATERIALS, DRT_FLAG_WATERTIGHT = 1, 2, 4, 8, 16
 
 _vp, _i, _u, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint32, ctypes.c_size_t
 _P = ctypes.POINTER

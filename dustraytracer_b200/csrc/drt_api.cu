@@ -108,7 +108,7 @@ struct drt_scene {
 	bool built = false;
 	DevBuf<WideNode> nodes;
 	DevBuf<drt_f4> nodes_f32;
-	DevBuf<drt_f4> tris, shade, materials, materials_ext;
+	DevBuf<drt_f4> tris, tris_v, shade, materials, materials_ext;
 	DevBuf<TexDesc> texdesc;
 	DevBuf<uint32_t> texels;
 	SceneView view;
@@ -462,10 +462,13 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* param
 			DRT_CUDA(scene->nodes_f32.alloc((size_t)res.wide_nodes * DRT_F32NODE_F4));
 			DRT_CUDA(launch_expand_nodes(scene->nodes.p, scene->nodes_f32.p, res.wide_nodes, stream));
 		}
+		// vertex records for the watertight test (48 B per triangle, leaf order)
+		DRT_CUDA(scene->tris_v.alloc(3 * n));
+		DRT_CUDA(launch_vertex_records(scene->tris.p, d_pos.p, scene->tris_v.p, (int)n, stream));
 		DRT_CUDA(cudaStreamSynchronize(stream));
 	}
 	else {
-		scene->nodes.release(); scene->nodes_f32.release(); scene->tris.release(); scene->shade.release();
+		scene->nodes.release(); scene->nodes_f32.release(); scene->tris.release(); scene->tris_v.release(); scene->shade.release();
 		DRT_CUDA(cudaStreamSynchronize(stream));
 	}
 
@@ -474,12 +477,13 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* param
 	v.tris = scene->tris.p; v.shade = scene->shade.p; v.materials = scene->materials.p; v.materials_ext = scene->materials_ext.p;
 	v.textures = scene->texdesc.p; v.texels = scene->texels.p;
 	v.nodes_f32 = scene->nodes_f32.p;
+	v.tris_v = scene->tris_v.p;
 	v.num_tris = (int32_t)n; v.num_nodes = res.wide_nodes; v.num_materials = (int32_t)mats.size(); v.num_textures = (int32_t)texdesc.size();
 	scene->stats.wide_nodes = (uint64_t)res.wide_nodes;
 	scene->stats.bvh2_nodes = (uint64_t)res.bvh2_nodes;
 	scene->stats.bvh_levels = (uint64_t)res.levels;
 	scene->stats.build_ms = build_ms;
-	scene->stats.device_bytes = scene->nodes.bytes() + scene->nodes_f32.bytes() + scene->tris.bytes() + scene->shade.bytes() + scene->materials.bytes()
+	scene->stats.device_bytes = scene->nodes.bytes() + scene->nodes_f32.bytes() + scene->tris.bytes() + scene->tris_v.bytes() + scene->shade.bytes() + scene->materials.bytes()
 		+ scene->texdesc.bytes() + scene->texels.bytes();
 	scene->built = true;
 	return DRT_OK;
@@ -752,7 +756,7 @@ static int autotune_pick(drt_renderer* r, const drt_scene* scene, const RenderPa
 {
 	probing = false;
 	if (!r->auto_variant || r->variant != 4 || (r->block_threads != 0 && r->block_threads != 128) || r->sched_bias[1] != 0 || (int64_t)P.n_samples > (int64_t)r->queue_max_spp) return -1;
-	if (P.shade.render_mode != 0 || (r->flags & DRT_FLAG_EXTENDED_MATERIALS) || P.width >= 65536 || P.height >= 65536) return -1;
+	if (P.shade.render_mode != 0 || (r->flags & (DRT_FLAG_EXTENDED_MATERIALS | DRT_FLAG_WATERTIGHT)) || P.width >= 65536 || P.height >= 65536) return -1;
 	drt_renderer::AutoTune& t = r->tune;
 	if (t.scene != scene || t.w != (uint32_t)P.width || t.h != (uint32_t)P.height || t.n != P.n_samples || t.flags != r->flags ||
 		t.bounce != P.shade.bounce_limit || t.sun != P.shade.enable_sunlight) {
@@ -783,6 +787,7 @@ static LaunchConfig launch_config(const drt_renderer* r)
 	cfg.rtl = (r->flags & DRT_FLAG_HOST_ARG_ORDER) != 0;
 	cfg.stats = (r->flags & DRT_FLAG_STATS) != 0;
 	cfg.ext_materials = (r->flags & DRT_FLAG_EXTENDED_MATERIALS) != 0;
+	cfg.watertight = (r->flags & DRT_FLAG_WATERTIGHT) != 0;
 	cfg.variant = r->variant; cfg.block_threads = r->block_threads;
 	cfg.auto_variant = r->auto_variant;
 	cfg.resident_sms = r->sm_count;

@@ -88,6 +88,9 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 		V3 acc = mk3(0.f, 0.f, 0.f);
 		if (valid) { const float4 a4 = P.accum[p]; acc = mk3(a4.x, a4.y, a4.z); }
 		__shared__ alignas(16) uint8_t lut[DRT_PERMUTE_LUT_BYTES];
+		if (VARIANT == 21) // variant 4 with the watertight TRI step (DRT_FLAG_WATERTIGHT; production arithmetic only)
+			acc = render_warp_phased<false, STATS, NODE_FMT_F32, false, LaneStack, true>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st, lut);
+		else
 		if (VARIANT == 17 || VARIANT == 18) {
 			__shared__ uint32_t stack_words[DRT_SSTACK_WORDS];
 			acc = render_warp_phased<STRICT, STATS, NODE_FMT_F32, VARIANT == 18, SharedLaneStack>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st, lut, stack_words);
@@ -241,7 +244,7 @@ __global__ void __launch_bounds__(256) k_trace_primary(const __grid_constant__ R
 // Ray-level parity probe (drt_trace_rays): caller-given rays through the SAME resumable steps the phased render kernels run
 // (node_step_f32 / node_step_q8 + tri_step / tri_step2 + trav_advance, drt_phased.cuh), one ray per thread, serial schedule.
 // anyhit = RayTest semantics (TraceRay.cu:35-38: first accepted hit ends the ray), else TraceRay closest hit.
-template <bool STRICT, int FMT, bool TRI2>
+template <bool STRICT, int FMT, bool TRI2, bool WT = false>
 __global__ void __launch_bounds__(128) k_trace_rays(const SceneView sc, const float* __restrict__ org, const float* __restrict__ dir, int n, bool anyhit, Hit* out)
 {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -262,7 +265,8 @@ __global__ void __launch_bounds__(128) k_trace_rays(const SceneView sc, const fl
 			phase = trav_advance(L, K);
 		}
 		else {
-			if (TRI2 ? tri_step2<STRICT, false>(sc, sc.tris, L, o, d, anyhit, nullptr) : tri_step<STRICT, false>(sc, sc.tris, L, o, d, anyhit, nullptr)) {
+			if (WT ? tri_step_wt<false>(sc, L, o, d, anyhit, nullptr)
+			       : (TRI2 ? tri_step2<STRICT, false>(sc, sc.tris, L, o, d, anyhit, nullptr) : tri_step<STRICT, false>(sc, sc.tris, L, o, d, anyhit, nullptr))) {
 				occluded = true;
 				phase = PH_SHADE;
 			}
@@ -306,6 +310,21 @@ __global__ void k_pack_rgb32f(float* out, const float4* accum, int n)
 	if (i >= n) return;
 	float4 a = accum[i];
 	out[3 * (size_t)i] = a.x; out[3 * (size_t)i + 1] = a.y; out[3 * (size_t)i + 2] = a.z;
+}
+
+// Vertex records of the leaf-order triangles for the watertight test: the builder's records hold v0 and two EDGES; a vertex
+// rebuilt as v0 + e would not be the same float in every triangle that shares it, so the original positions are fetched again.
+__global__ void k_vertex_records(const drt_f4* tris, const float* pos, drt_f4* out, int n)
+{
+	const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+	if (slot >= n) return;
+	const drt_f4 r0 = tris[3 * (size_t)slot], r1 = tris[3 * (size_t)slot + 1];
+	const float* p = pos + 9 * (size_t)as_uint(r0.w);
+	drt_f4 a, b, c;
+	a.x = p[0]; a.y = p[1]; a.z = p[2]; a.w = r0.w;
+	b.x = p[3]; b.y = p[4]; b.z = p[5]; b.w = r1.w;
+	c.x = p[6]; c.y = p[7]; c.z = p[8]; c.w = 0.f;
+	out[3 * (size_t)slot] = a; out[3 * (size_t)slot + 1] = b; out[3 * (size_t)slot + 2] = c;
 }
 
 __global__ void k_expand_nodes(const WideNode* wide, drt_f4* out, int n)
@@ -505,6 +524,12 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 		return cudaGetLastError();
 	}
 	if (variant >= 2 && P.shade.render_mode != DRT_RENDER_NORMAL) variant = 1;
+	// DRT_FLAG_WATERTIGHT: the watertight TRI step replaces the reference's Moller-Trumbore; not in parity (STRICT) mode, whose
+	// whole point is the reference's predicate, and only where the scene has vertex records and expanded nodes
+	if (cfg.watertight && !STRICT && variant >= 2 && P.scene.tris_v != nullptr && P.scene.nodes_f32 != nullptr && threads == 128) {
+		k_render<false, STATS, 21><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+		return cudaGetLastError();
+	}
 	// variant 16: block-level regrouping (no statistics build of it: counted launches run the per-warp voting kernel)
 	if (variant == 16) {
 		if (!STATS && P.work_queue != nullptr && cfg.resident_sms > 0 && P.tile_stride > 0 && P.width < 65536 && P.height < 65536) return launch_regroup<STRICT>(P, cfg, s);
@@ -594,6 +619,10 @@ cudaError_t launch_trace_rays(const SceneView& sc, const float* org_dev, const f
 	const unsigned blocks = (unsigned)((n + 127) / 128);
 	const bool f32 = sc.nodes_f32 != nullptr && cfg.variant != 3 && cfg.variant != 7 && cfg.variant != 8 && cfg.variant != 10 && cfg.variant != 14;
 	const bool tri2 = cfg.variant == 15 || (cfg.auto_variant && sc.num_tris >= DRT_TRI2_MIN_TRIS);
+	if (cfg.watertight && !cfg.strict && f32 && sc.tris_v != nullptr) {
+		k_trace_rays<false, NODE_FMT_F32, false, true><<<blocks, 128, 0, s>>>(sc, org_dev, dir_dev, n, anyhit, out_dev);
+		return cudaGetLastError();
+	}
 #define DRT_TR(S, F, T2) k_trace_rays<S, F, T2><<<blocks, 128, 0, s>>>(sc, org_dev, dir_dev, n, anyhit, out_dev)
 	if (cfg.strict) { if (f32) { if (tri2) DRT_TR(true, NODE_FMT_F32, true); else DRT_TR(true, NODE_FMT_F32, false); } else { if (tri2) DRT_TR(true, NODE_FMT_Q8, true); else DRT_TR(true, NODE_FMT_Q8, false); } }
 	else { if (f32) { if (tri2) DRT_TR(false, NODE_FMT_F32, true); else DRT_TR(false, NODE_FMT_F32, false); } else { if (tri2) DRT_TR(false, NODE_FMT_Q8, true); else DRT_TR(false, NODE_FMT_Q8, false); } }
@@ -619,6 +648,13 @@ cudaError_t launch_pack_rgb32f(float* out, const drt_f4* accum, int n, cudaStrea
 {
 	if (n <= 0) return cudaSuccess;
 	k_pack_rgb32f<<<(n + 255) / 256, 256, 0, s>>>(out, accum, n);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_vertex_records(const drt_f4* tris, const float* pos, drt_f4* out, int n, cudaStream_t s)
+{
+	if (n <= 0) return cudaSuccess;
+	k_vertex_records<<<(n + 255) / 256, 256, 0, s>>>(tris, pos, out, n);
 	return cudaGetLastError();
 }
 

@@ -21,6 +21,7 @@ struct LaunchConfig {
 	bool strict = false;  // DRT_FLAG_STRICT
 	bool rtl = false;     // DRT_FLAG_HOST_ARG_ORDER
 	bool stats = false;   // DRT_FLAG_STATS
+	bool watertight = false; // DRT_FLAG_WATERTIGHT: watertight TRI step (production arithmetic only)
 	bool ext_materials = false; // DRT_FLAG_EXTENDED_MATERIALS: emissive / metal / dielectric shading (reference-shaped loop kernel)
 	int variant = 4;      // render kernel variant (see drt_kernels.cu); 4 = default
 	bool auto_variant = false; // variant 4 was not asked for explicitly: scenes of DRT_TRI2_MIN_TRIS triangles or more run variant 15
@@ -32,6 +33,7 @@ struct LaunchConfig {
 // Bytes of the regrouping kernel's traversal-stack overflow area for a device of `sms` multiprocessors (RenderParams::rg_overflow).
 size_t regroup_overflow_bytes(int sms);
 cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s);
+cudaError_t launch_vertex_records(const drt_f4* tris, const float* pos, drt_f4* out, int n, cudaStream_t s);
 cudaError_t launch_expand_nodes(const WideNode* wide, drt_f4* out_f32, int n, cudaStream_t s);
 cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches);
 cudaError_t launch_trace_primary(const RenderParams& P, uint32_t frame_index, Hit* out_dev, const LaunchConfig& cfg, cudaStream_t s);

@@ -378,6 +378,100 @@ DRT_HD bool tri_step(const SceneView& sc, const drt_f4* tris, LaneTrav& L, V3 o,
 	return false;
 }
 
+// ---- watertight ray / triangle test (production mode only, DRT_FLAG_WATERTIGHT; north_star subsystem 3) ----
+// The reference's Moller-Trumbore (Intersection.cu:4-36, what STRICT mode must keep) has two leaks: an ABSOLUTE epsilon on the
+// determinant (|det| < 1e-6, Common/physical_units.hpp:12, Intersection.cu:13), which drops every triangle that is small or
+// far away, and per-triangle edge functions, which can round to "outside" on BOTH sides of a shared edge. This is the test of
+// Woop, Benthin, Wald, "Watertight Ray/Triangle Intersection" (JCGT 2013): the ray is sheared onto its major axis, the three
+// edge functions are differences of two separately rounded products of vertex coordinates that are computed the same way
+// whichever triangle the edge belongs to (so a ray cannot pass between two triangles that share the edge: one of them gets
+// U, V, W of one sign or zero), with a double-precision recomputation when an edge function is exactly zero.
+struct RayShear {
+	int kx, ky, kz;
+	float sx, sy, sz;
+};
+DRT_HD float v3_comp(V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+DRT_HD RayShear ray_shear_setup(V3 d)
+{
+	RayShear r;
+	const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+	r.kz = ax > ay ? (ax > az ? 0 : 2) : (ay > az ? 1 : 2);
+	r.kx = r.kz == 2 ? 0 : r.kz + 1;
+	r.ky = r.kx == 2 ? 0 : r.kx + 1;
+	const float dz = v3_comp(d, r.kz);
+	if (dz < 0.f) { const int t = r.kx; r.kx = r.ky; r.ky = t; } // keep the winding
+	r.sx = v3_comp(d, r.kx) / dz; r.sy = v3_comp(d, r.ky) / dz; r.sz = 1.0f / dz;
+	return r;
+}
+DRT_HD float wt_mul(float a, float b)
+{
+#if defined(__CUDA_ARCH__)
+	return __fmul_rn(a, b); // never contracted into an FMA: a*b - c*d must be the exact negative of c*d - a*b
+#else
+	return a * b;
+#endif
+}
+DRT_HD float wt_sub(float a, float b)
+{
+#if defined(__CUDA_ARCH__)
+	return __fsub_rn(a, b);
+#else
+	return a - b;
+#endif
+}
+
+// TRI step with the watertight predicate on the vertex records (sc.tris_v). Same bookkeeping as tri_step: closest hit with
+// exact-t ties to the lowest canonical id, any-hit ends at the first accepted triangle, alpha cut-out on the barycentrics
+// (u = weight of v1, v = weight of v2, like Intersection.cu:31). Keeps the reference's t > 1e-6 (self-hit guard), drops its
+// determinant epsilon.
+template <bool STATS>
+DRT_HD bool tri_step_wt(const SceneView& sc, LaneTrav& L, V3 o, V3 d, bool anyhit, TraceStats* st)
+{
+	const int k = lo_bit(L.tri_bits);
+	L.tri_bits &= L.tri_bits - 1u;
+	const int slot = (int)(L.tri_base + (uint32_t)k);
+	const drt_f4* tp = sc.tris_v + 3 * (size_t)slot;
+	const drt_f4 r0 = ld_f4(tp), r1 = ld_f4(tp + 1), r2 = ld_f4(tp + 2);
+	if (STATS && st) st->tris++;
+	const RayShear R = ray_shear_setup(d);
+	const V3 A = mk3(r0.x - o.x, r0.y - o.y, r0.z - o.z), B = mk3(r1.x - o.x, r1.y - o.y, r1.z - o.z), C = mk3(r2.x - o.x, r2.y - o.y, r2.z - o.z);
+	const float Akz = v3_comp(A, R.kz), Bkz = v3_comp(B, R.kz), Ckz = v3_comp(C, R.kz);
+	const float Ax = wt_sub(v3_comp(A, R.kx), wt_mul(R.sx, Akz)), Ay = wt_sub(v3_comp(A, R.ky), wt_mul(R.sy, Akz));
+	const float Bx = wt_sub(v3_comp(B, R.kx), wt_mul(R.sx, Bkz)), By = wt_sub(v3_comp(B, R.ky), wt_mul(R.sy, Bkz));
+	const float Cx = wt_sub(v3_comp(C, R.kx), wt_mul(R.sx, Ckz)), Cy = wt_sub(v3_comp(C, R.ky), wt_mul(R.sy, Ckz));
+	float U = wt_sub(wt_mul(Cx, By), wt_mul(Cy, Bx));
+	float V = wt_sub(wt_mul(Ax, Cy), wt_mul(Ay, Cx));
+	float W = wt_sub(wt_mul(Bx, Ay), wt_mul(By, Ax));
+	if (U == 0.f || V == 0.f || W == 0.f) { // on an edge in fp32: decide in double (the products are exact there)
+		U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+		V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+		W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+	}
+	if ((U < 0.f || V < 0.f || W < 0.f) && (U > 0.f || V > 0.f || W > 0.f)) return false;
+	const float det = U + V + W;
+	if (det == 0.f) return false;
+	const float T = U * (R.sz * Akz) + V * (R.sz * Bkz) + W * (R.sz * Ckz);
+	const float rdet = 1.0f / det;
+	const float t = T * rdet;
+	if (!(t > DRT_TRIANGLE_EPSILON)) return false;
+	const float u = V * rdet, v = W * rdet;
+	const uint32_t matw = as_uint(r1.w);
+	if (anyhit) {
+		if ((matw & 0x80000000u) && !alpha_accept<false>(sc, slot, matw & 0x7fffffffu, u, v, st)) return false;
+		L.hit.prim = slot; L.hit.t = t;
+		return true;
+	}
+	if (!(t < L.hit.t)) {
+		if (!(t == L.hit.t) || L.hit.prim < 0) return false;
+		if (st) st->ties++;
+		const uint32_t id = as_uint(r0.w), best_id = as_uint(ld_f4(sc.tris_v + 3 * (size_t)L.hit.prim).w);
+		if (!(id < best_id)) return false;
+	}
+	if ((matw & 0x80000000u) && !alpha_accept<false>(sc, slot, matw & 0x7fffffffu, u, v, st)) return false;
+	L.hit.prim = slot; L.hit.t = t;
+	return false;
+}
+
 // Geometric part of one Moller-Trumbore test, computed unconditionally (Intersection.cu:8-33, the reference's operation
 // order; a rejected triangle may produce inf / NaN in t, u, v, which nobody reads).
 struct TriGeo {
@@ -637,7 +731,7 @@ __device__ __forceinline__ void stack_bind(LaneStack&, uint32_t*) {}
 __device__ __forceinline__ void stack_bind(SharedLaneStack& K, uint32_t* words) { K.s = words + threadIdx.x; }
 
 // One warp: every lane owns one pixel (valid or not) for all samples of the launch.
-template <bool STRICT, bool STATS, int FMT, bool TRI2 = false, class STACK = LaneStack>
+template <bool STRICT, bool STATS, int FMT, bool TRI2 = false, class STACK = LaneStack, bool WT = false>
 __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const PhasedTuning T, uint32_t x, uint32_t y, bool valid,
 	bool rtl, V3 acc, PathCounters& pc, TraceStats* st, uint8_t* lut, uint32_t* stack_words = nullptr)
 {
@@ -679,8 +773,9 @@ __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const Ph
 					phase = trav_advance(L, K);
 				}
 				else if (pick == PH_TRI) {
-					if (TRI2 ? tri_step2<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)
-					         : tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)) phase = PH_SHADE;
+					if (WT ? tri_step_wt<STATS>(P.scene, L, S.o, S.d, S.shadow, st)
+					       : (TRI2 ? tri_step2<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st)
+					               : tri_step<STRICT, STATS>(P.scene, P.scene.tris, L, S.o, S.d, S.shadow, st))) phase = PH_SHADE;
 					else phase = trav_advance(L, K);
 				}
 				else {

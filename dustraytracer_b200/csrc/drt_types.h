@@ -54,6 +54,7 @@ struct SceneView {
 	const uint32_t* texels;
 	int32_t num_tris, num_nodes, num_materials, num_textures;
 	const drt_f4* nodes_f32; // expanded 256-byte nodes (drt_phased.cuh) or null: built for cache-resident scenes only
+	const drt_f4* tris_v;    // 48 B per leaf-order slot: the three VERTICES (v0 | id, v1 | material word, v2 | 0) for the watertight test
 };
 
 // Camera terms that do not depend on the pixel, evaluated once on the host in the reference's

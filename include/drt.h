@@ -112,6 +112,11 @@ typedef enum drt_flags {
 	DRT_FLAG_STRICT = 1,       /* separately-rounded fp32 in the reference's operation order (parity mode)      */
 	DRT_FLAG_HOST_ARG_ORDER = 2, /* draw randomUnitVec3 components right-to-left like the g++-compiled oracle     */
 	DRT_FLAG_STATS = 4,        /* count node visits / triangle tests (slower; for the roofline's V and T terms) */
+	DRT_FLAG_WATERTIGHT = 16,  /* production arithmetic only (ignored with DRT_FLAG_STRICT): the watertight ray / triangle test of Woop,
+	                              Benthin, Wald (JCGT 2013) replaces the reference's Moller-Trumbore (Intersection.cu:4-36), whose
+	                              absolute determinant epsilon (1e-6, physical_units.hpp:12) drops small / distant triangles and
+	                              whose per-triangle edge tests can leak between triangles that share an edge. Changes which
+	                              rays hit near edges, so it is OFF by default and off in parity mode. */
 	DRT_FLAG_EXTENDED_MATERIALS = 8 /* opt-in, beyond the reference: shade the material fields the
 	                              reference loads but ignores (Material.cuh:10-22; RayGen.cuh never reads them):
 	                              emissive_factor, metallic + roughness (mirror / fuzzy reflection), transmission +

@@ -306,3 +306,106 @@ def test_regrouping_kernel_matches_the_megakernel(drt, name, size):
     print("%s production mode, variant 16 vs 4 at 64 spp: RMSE %.2e, mean %+.1e, rays %d vs %d" % (name, np.sqrt((diff ** 2).mean()), diff.mean(), rays, rays4))
     assert np.sqrt((diff ** 2).mean()) <= 0.02 and abs(diff.mean()) <= 2e-3
     assert abs(rays - rays4) <= 0.005 * rays4 + 8
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# watertight ray / triangle test (DRT_FLAG_WATERTIGHT, production mode only)
+# ---------------------------------------------------------------------------------------------------------------------
+def _grid_mesh(n, size, z, jitter, seed):
+    """n x n quads (2 triangles each) spanning [-size/2, size/2]^2 at depth z, interior vertices jittered in x, y and z:
+    a closed sheet -- every ray through its interior must hit it."""
+    rng = np.random.RandomState(seed)
+    g = np.linspace(-size / 2, size / 2, n + 1)
+    vx, vy = np.meshgrid(g, g, indexing="xy")
+    v = np.stack([vx, vy, np.full_like(vx, z)], -1).astype(np.float64)
+    cell = size / n
+    v[1:-1, 1:-1, 0:2] += rng.uniform(-jitter, jitter, (n - 1, n - 1, 2)) * cell
+    v[1:-1, 1:-1, 2] += rng.uniform(-jitter, jitter, (n - 1, n - 1)) * cell
+    v = v.astype(np.float32)
+    a, b, c, d = v[:-1, :-1], v[:-1, 1:], v[1:, :-1], v[1:, 1:]
+    tris = np.concatenate([np.stack([a, b, d], 2).reshape(-1, 9), np.stack([a, d, c], 2).reshape(-1, 9)], 0)
+    return v, np.ascontiguousarray(tris, np.float32)
+
+
+def test_watertight_mode_closes_the_cracks_of_moller_trumbore(drt):
+    """Rays aimed EXACTLY at the vertices and at points on the shared edges of a jittered triangle sheet (the directions are
+    vertex - origin in fp32): with the reference's Moller-Trumbore some of them slip between two triangles; the watertight
+    test must not lose one. A second sheet of tiny triangles (cell 3e-4 at distance 1: |det| < 1e-6) shows the other leak, the
+    absolute determinant epsilon (Intersection.cu:13): the reference predicate misses the whole sheet. STRICT mode ignores
+    the flag (parity mode is the reference's predicate) and renders the same bits with and without it."""
+    WT = 16
+    o = np.array([0.013, -0.007, 0.0], np.float32)
+    v, tris = _grid_mesh(48, 2.0, -3.0, 0.15, 1)   # (jitter small enough that the sheet never folds over as seen from the origin)
+    s = drt.Scene.from_triangles(tris)
+    s.build_bvh()
+    inner = v[4:-4, 4:-4].reshape(-1, 3)
+    rng = np.random.RandomState(2)
+    # vertices, and points on horizontal / vertical / diagonal edges (p = w * a + (1 - w) * b of two vertices a, b of an edge)
+    m = 6000
+    i, j = rng.randint(3, 45, m), rng.randint(3, 45, m)
+    kind = rng.randint(0, 3, m)
+    di, dj = np.where(kind == 0, 0, 1), np.where(kind == 1, 0, 1)   # (0,1) horizontal, (1,0) vertical, (1,1) diagonal
+    w = rng.uniform(0.05, 0.95, (m, 1)).astype(np.float32)
+    on_edges = v[i, j] * w + v[i + di, j + dj] * (np.float32(1) - w)
+    targets = np.concatenate([inner, on_edges], 0).astype(np.float32)
+    d = (targets - o).astype(np.float32)
+    org = np.repeat(o[None], len(d), 0)
+    r_mt, r_wt = drt.Renderer(), drt.Renderer(flags=WT)
+    h_mt = r_mt.trace_rays(s, org, d)
+    h_wt = r_wt.trace_rays(s, org, d)
+    miss_mt, miss_wt = int((h_mt["prim_id"] < 0).sum()), int((h_wt["prim_id"] < 0).sum())
+    print("edge / vertex rays: %d, Moller-Trumbore misses %d, watertight misses %d" % (len(d), miss_mt, miss_wt))
+    assert miss_wt == 0
+    # where both hit, they agree on the distance (the triangle may be either neighbour of the edge)
+    both = (h_mt["prim_id"] >= 0) & (h_wt["prim_id"] >= 0)
+    assert np.abs(h_mt["t"][both] - h_wt["t"][both]).max() <= 1e-4
+    # any-hit rays (shadow rays) through the same points are occluded in watertight mode
+    assert (r_wt.trace_rays(s, org, d, anyhit=True)["prim_id"] >= 0).all()
+    # the absolute-epsilon leak: a sheet of tiny triangles
+    v2, tris2 = _grid_mesh(64, 64 * 3e-4, -1.0, 0.15, 3)
+    s2 = drt.Scene.from_triangles(tris2)
+    s2.build_bvh()
+    t2 = (v2[8:-8, 8:-8].reshape(-1, 3) + np.float32([1e-5, 2e-5, 0])).astype(np.float32)
+    d2 = (t2 - o * 0).astype(np.float32)
+    o2 = np.zeros_like(d2)
+    m_mt = int((r_mt.trace_rays(s2, o2, d2)["prim_id"] < 0).sum())
+    m_wt = int((r_wt.trace_rays(s2, o2, d2)["prim_id"] < 0).sum())
+    print("tiny-triangle sheet: %d rays, Moller-Trumbore misses %d, watertight misses %d" % (len(d2), m_mt, m_wt))
+    assert m_wt == 0 and m_mt > len(d2) // 2
+    # rendering: watertight production images agree with the plain production images up to the few edge pixels, and STRICT ignores the flag
+    scene = gpu_scene(drt, "room")
+    st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=4, max_samples=100000)
+
+    def render(flags, variant=-1):
+        r = drt.Renderer(flags=flags)
+        r.set_tuning(variant, 0)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(160, 90)
+        r.Render(drt.Camera(), scene, 32)
+        return r.readback(drt.DRT_ACCUM_RGB32F) / 32, r.counters()
+
+    a0, c0 = render(0)
+    a1, c1 = render(WT)
+    diff = a1.astype(np.float64) - a0
+    print("room 160x90x32: watertight vs Moller-Trumbore RMSE %.2e, mean %+.1e, rays %d vs %d" % (
+        np.sqrt((diff ** 2).mean()), diff.mean(), c1["closest_rays"] + c1["shadow_rays"], c0["closest_rays"] + c0["shadow_rays"]))
+    assert np.sqrt((diff ** 2).mean()) <= 0.02 and abs(diff.mean()) <= 2e-3
+    # ... and the flag does reach the render kernels: the tiny-triangle sheet is invisible to Moller-Trumbore and solid when watertight
+    v3, tris3 = _grid_mesh(256, 256 * 3e-4, -1.0, 0.15, 4)
+    s3 = drt.Scene.from_triangles(tris3)
+    s3.build_bvh()
+    closest = {}
+    for flags in (0, WT):
+        r = drt.Renderer(flags=flags)
+        r.m_RendererSettings = drt.RendererSettings(enable_sunlight=0, ray_bounce_limit=1, max_samples=100000)
+        r.ResizeBuffer(160, 90)
+        r.Render(drt.Camera(pos=(0, 0, 0)), s3, 4)
+        closest[flags] = r.counters()["closest_rays"]   # a primary hit scatters a second closest-hit ray
+    print("tiny-triangle sheet rendered: closest-hit rays Moller-Trumbore %d (= %d primary rays), watertight %d" % (closest[0], 160 * 90 * 4, closest[WT]))
+    assert closest[0] == 160 * 90 * 4 and closest[WT] >= closest[0] + 32
+    s0, _ = render(STRICT)
+    s1, _ = render(STRICT | WT)
+    assert np.array_equal(bits(s0), bits(s1))
+    # the pixel-queue and regrouping kernels do not have the watertight step: the flag wins over an explicit variant
+    a9, c9 = render(WT, 9)
+    assert np.array_equal(bits(a9), bits(a1)) and c9 == c1
