@@ -453,6 +453,10 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* param
 		}
 		build_ms = ms;
 		if (res.tris_emitted != (int)n) return fail(DRT_ERR_CUDA, "BVH build emitted " + std::to_string(res.tris_emitted) + " of " + std::to_string(n) + " triangles");
+		// The render kernels keep DRT_PSTACK traversal-stack entries per lane and push at most one entry (the rest of a node group)
+		// per level of the wide tree: a tree deeper than that could lose subtrees, so it is refused here rather than rendered wrong.
+		if (res.wide_levels > DRT_PSTACK)
+			return fail(DRT_ERR_INVALID, "BVH has " + std::to_string(res.wide_levels) + " wide levels, more than the " + std::to_string(DRT_PSTACK) + "-entry traversal stack of the render kernels");
 		// keep only the wide nodes that exist
 		DRT_CUDA(scene->nodes.alloc((size_t)res.wide_nodes));
 		DRT_CUDA(cudaMemcpyAsync(scene->nodes.p, wide_tmp.p, (size_t)res.wide_nodes * sizeof(WideNode), cudaMemcpyDeviceToDevice, stream));

@@ -153,10 +153,12 @@ int load_gltf(const char* path, HostScene& out, std::string& err, unsigned flags
 	for (size_t i = 0; i < jviews.size(); i++) {
 		const JsonValue& v = jviews.arr[i];
 		views[i].buffer = v.get_int("buffer", 0);
-		views[i].offset = (size_t)v.get_num("byteOffset", 0);
-		views[i].length = (size_t)v.get_num("byteLength", 0);
-		views[i].stride = (size_t)v.get_num("byteStride", 0);
-		if (views[i].buffer < 0 || (size_t)views[i].buffer >= bdata.size() || views[i].offset + views[i].length > blen[views[i].buffer]) {
+		if (!v.get_size("byteOffset", 0, &views[i].offset) || !v.get_size("byteLength", 0, &views[i].length) || !v.get_size("byteStride", 0, &views[i].stride)) {
+			err = "bufferView with a negative, fractional or huge byte range"; return DRT_ERR_FORMAT;
+		}
+		// (offset <= size first, then length against what is left: the sum could wrap)
+		if (views[i].buffer < 0 || (size_t)views[i].buffer >= bdata.size() || views[i].offset > blen[views[i].buffer]
+			|| views[i].length > blen[views[i].buffer] - views[i].offset || views[i].stride > 65536) {
 			err = "bufferView out of range"; return DRT_ERR_FORMAT;
 		}
 	}
@@ -249,7 +251,8 @@ int load_gltf(const char* path, HostScene& out, std::string& err, unsigned flags
 			}
 			const int comp = jacc.arr[a_idx].get_int("componentType", 5123);
 			if (comp != 5123) { err = "index componentType " + std::to_string(comp) + ": the reference loader reads unsigned short only (Scene.cu:161)"; return DRT_ERR_FORMAT; }
-			const size_t idx_count_accessor = (size_t)jacc.arr[a_idx].get_num("count", 0);
+			size_t idx_count_accessor = 0;
+			if (!jacc.arr[a_idx].get_size("count", 0, &idx_count_accessor)) { err = "index accessor with a bad count"; return DRT_ERR_FORMAT; }
 			const View& iv = views[v_idx];
 			const uint8_t* buf = bdata[iv.buffer];
 			const size_t buf_len = blen[iv.buffer];
@@ -263,7 +266,8 @@ int load_gltf(const char* path, HostScene& out, std::string& err, unsigned flags
 				for (int k = 0; k < 3; k++) {
 					uint16_t vi;
 					memcpy(&vi, buf + 2 * (i_begin + 3 * t + k), 2);
-					if (o_pos + 12 * ((size_t)vi + 1) > buf_len || o_nrm + 12 * ((size_t)vi + 1) > buf_len || o_uv + 8 * ((size_t)vi + 1) > buf_len) {
+					// (o_* <= buf_len was checked with the bufferViews; vi < 65536, so the products cannot wrap)
+					if (12 * ((size_t)vi + 1) > buf_len - o_pos || 12 * ((size_t)vi + 1) > buf_len - o_nrm || 8 * ((size_t)vi + 1) > buf_len - o_uv) {
 						err = "vertex index out of buffer range"; return DRT_ERR_FORMAT;
 					}
 					memcpy(p9 + 3 * k, buf + o_pos + 12 * (size_t)vi, 12);

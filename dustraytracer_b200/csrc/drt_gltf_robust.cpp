@@ -69,7 +69,7 @@ bool resolve_accessor(const Doc& D, int a, Accessor& A, std::string& err)
 	if (ja.has("sparse")) { err = "sparse accessors are not supported"; return false; }
 	A.comp = ja.get_int("componentType", 0);
 	A.ncomp = type_comps(ja.get_str("type"));
-	A.count = (size_t)ja.get_num("count", 0);
+	if (!ja.get_size("count", 0, &A.count) || A.count > ((size_t)1 << 40)) { err = "accessor " + std::to_string(a) + ": bad count"; return false; }
 	const JsonValue* nv = ja.get("normalized");
 	A.normalized = nv && nv->type == JsonValue::Bool && nv->b;
 	const int cs = comp_size(A.comp);
@@ -79,9 +79,13 @@ bool resolve_accessor(const Doc& D, int a, Accessor& A, std::string& err)
 	if (bv < 0) { A.base = nullptr; A.stride = elem; return true; }
 	if ((size_t)bv >= D.views.size()) { err = "accessor " + std::to_string(a) + ": bufferView out of range"; return false; }
 	const RView& v = D.views[bv];
-	const size_t off = (size_t)ja.get_num("byteOffset", 0);
+	size_t off = 0;
+	if (!ja.get_size("byteOffset", 0, &off)) { err = "accessor " + std::to_string(a) + ": bad byteOffset"; return false; }
 	A.stride = v.stride ? v.stride : elem;
-	if (A.count && off + A.stride * (A.count - 1) + elem > v.length) { err = "accessor " + std::to_string(a) + " runs past its bufferView"; return false; }
+	// off + stride * (count - 1) + elem <= length, written so that nothing can wrap (stride <= 65536, count <= 2^40)
+	if (A.count && (off > v.length || elem > v.length - off || (A.count - 1) > (v.length - off - elem) / A.stride)) {
+		err = "accessor " + std::to_string(a) + " runs past its bufferView"; return false;
+	}
 	A.base = (*D.bdata)[v.buffer] + v.offset + off;
 	return true;
 }
@@ -295,7 +299,9 @@ int emit_robust_geometry(const JsonValue& root, const std::vector<const uint8_t*
 	W.doc.views.resize(jviews.size());
 	for (size_t i = 0; i < jviews.size(); i++) { // ranges were validated by load_gltf
 		const JsonValue& v = jviews.arr[i];
-		W.doc.views[i] = RView{ v.get_int("buffer", 0), (size_t)v.get_num("byteOffset", 0), (size_t)v.get_num("byteLength", 0), (size_t)v.get_num("byteStride", 0) };
+		RView rv{ v.get_int("buffer", 0), 0, 0, 0 };
+		v.get_size("byteOffset", 0, &rv.offset); v.get_size("byteLength", 0, &rv.length); v.get_size("byteStride", 0, &rv.stride); // (validated by load_gltf)
+		W.doc.views[i] = rv;
 	}
 	// roots: the default scene's, else scene 0's, else every node that is nobody's child
 	std::vector<int> roots;

@@ -29,7 +29,16 @@ struct JsonValue {
 	int get_int(const char* key, int dflt) const
 	{
 		const JsonValue* v = get(key);
-		return (v && v->type == Number) ? (int)v->num : dflt;
+		return (v && v->type == Number && v->num >= -2147483648.0 && v->num <= 2147483647.0) ? (int)v->num : dflt; // (a cast out of range is undefined)
+	}
+	// A JSON number meant as a byte offset / length / count: true and *out set when it is a finite integer-valued number in
+	// [0, 2^53] (a cast of anything else to size_t is undefined behaviour); a missing key gives dflt.
+	bool get_size(const char* key, size_t dflt, size_t* out) const
+	{
+		const double v = get_num(key, (double)dflt);
+		if (!(v >= 0.0) || !(v <= 9007199254740992.0)) return false; // (also rejects NaN)
+		*out = (size_t)v;
+		return true;
 	}
 	double get_num(const char* key, double dflt) const
 	{

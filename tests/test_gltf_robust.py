@@ -313,6 +313,44 @@ def test_robust_errors_are_reported_not_crashes(tmp_path):
     assert s.stats()["triangles"] == 1
 
 
+def test_crafted_byte_ranges_are_rejected_not_wrapped(tmp_path):
+    """Offsets / lengths / counts that are negative, fractional-huge or whose SUM wraps size_t must fail with a format error in
+    both loaders (a cast of such a double to size_t is undefined; `offset + length > size` wraps)."""
+    def base():
+        g = Glb()
+        pa = g.accessor(np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32))
+        na = g.accessor(np.array([[0, 0, 1]] * 3, np.float32))
+        ta = g.accessor(np.zeros((3, 2), np.float32))
+        ia = g.accessor(np.array([0, 1, 2], np.uint16))
+        g.j["meshes"] = [{"primitives": [{"attributes": {"POSITION": pa, "NORMAL": na, "TEXCOORD_0": ta}, "indices": ia}]}]
+        g.j["nodes"] = [{"mesh": 0}]
+        return g, pa, ia
+
+    g, pa, ia = base()
+    assert load(g.write(tmp_path / "ok.glb")).stats()["triangles"] == 1 and load(str(tmp_path / "ok.glb"), robust=False).stats()["triangles"] == 1
+    cases = []
+    for key, val in (("byteOffset", -4), ("byteOffset", 1.8446744073709552e19), ("byteLength", 1.8446744073709552e19), ("byteLength", -1),
+                     ("byteOffset", 1e300), ("byteStride", 1e18)):
+        g, pa, ia = base()
+        g.j["bufferViews"][0][key] = val
+        cases.append(("view_%s_%g" % (key, val), g))
+    g, pa, ia = base()
+    g.j["bufferViews"][0]["byteOffset"] = 2 ** 64 - 8   # offset + length wraps to a small number
+    g.j["bufferViews"][0]["byteLength"] = 36
+    cases.append(("view_wrap", g))
+    for robust in (True, False):
+        for name, g in cases:
+            with pytest.raises(drt.DrtError) as e:
+                load(g.write(tmp_path / (name + ".glb")), robust=robust)
+            assert e.value.code == -3, (name, robust, str(e.value))
+    for key, val in (("count", -3), ("count", 1e300), ("byteOffset", -12), ("byteOffset", 1.8446744073709552e19), ("count", 2 ** 62)):
+        g, pa, ia = base()
+        g.j["accessors"][pa][key] = val
+        with pytest.raises(drt.DrtError) as e:
+            load(g.write(tmp_path / "acc.glb"))
+        assert e.value.code == -3, (key, val, str(e.value))
+
+
 @pytest.mark.gpu
 def test_robust_scene_renders_like_the_same_soup_given_directly(tmp_path):
     """A transformed, strided, u32-indexed file loaded with DRT_LOAD_ROBUST traces exactly like the world-space

@@ -477,7 +477,7 @@ def test_stats_counters(drt):
     r.Render(drt.Camera(), scene, 2)
     c = r.counters()
     rays = c["closest_rays"] + c["shadow_rays"]
-    assert rays > 0 and c["node_visits"] >= rays and c["tri_tests"] > 0 and c["max_stack"] <= 48
+    assert rays > 0 and c["node_visits"] >= rays and c["tri_tests"] > 0 and c["max_stack"] <= 32  # DRT_PSTACK of the production kernels
     print("room: %.2f wide-node visits/ray, %.2f triangle tests/ray" % (c["node_visits"] / rays, c["tri_tests"] / rays))
 
 
