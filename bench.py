@@ -532,7 +532,7 @@ def run_ours(args, rank, world, local_rank):
                     "thread_instructions_per_ray": tipr, "warp_instructions_per_ray": (ncu["warp_inst"] / capture_rays) if tipr and ncu.get("warp_inst") else None,
                     "capture": {k: ncu.get(k) for k in ("source", "spp", "duration_ms", "issue_slot_fraction", "active_lanes_per_instruction", "local_sectors")},
                     "peak_note": "148 SMs x 4 schedulers x 32 lanes x %.0f MHz (SM clock sampled during the timed region)" % sm_mhz,
-                    "kernel": "k_render<STRICT=0,STATS=0,VARIANT=%d> (phased, one launch per step)" % max(4, int(os.environ.get("DRT_VARIANT", "4"))),
+                    "kernel": "k_render<STRICT=0,STATS=0,VARIANT=%d> (per-warp phase voting, one launch per step; 22 = with the sample pool)" % r.last_variant(),
                     "algorithmic_bw": algorithmic_bw}
         # ---- CPU baseline: bounded sample on the host cores (child process under a wall budget), and the parity of the GPU's
         #      first frames of the SAME image against the frames the CPU just rendered ----

@@ -290,6 +290,10 @@ class Renderer:
     def kernel_launches(self):
         return _lib.lib().drt_renderer_kernel_launches(self._h)
 
+    def last_variant(self):
+        """Kernel variant the last Render ran (automatic selection resolved)."""
+        return _lib.lib().drt_renderer_last_variant(self._h)
+
     def trace_primary(self, cam, scene, frame_index=1):
         """Parity probe: structured array (prim_id, t, u, v) per pixel, p = x + y*W."""
         w, h = self.getBufferWidth(), self.getBufferHeight()

@@ -131,6 +131,7 @@ struct drt_renderer {
 	void* ipc_display = nullptr;
 	DevBuf<Counters> counters;
 	DevBuf<unsigned> work_queue; // pixel-queue kernel: next tile, warps that have left (the kernel leaves both at zero)
+	DevBuf<uint8_t> pool_scratch; // sample-pool kernel (variants 22 / 23): pool colours of a launch, grown on demand
 	DevBuf<uint8_t> rg_overflow; // regrouping kernel (variant 16): traversal-stack overflow area, allocated at its first launch
 	DevBuf<Hit> hits;
 	DevBuf<uint8_t> staging;
@@ -162,6 +163,7 @@ struct drt_renderer {
 	} tune;
 	int sm_count = 0;
 	int kernel_launches = 0;
+	int last_variant = -1; // kernel variant of the last render launch (after automatic selection)
 };
 
 static void fill_stats(drt_scene* s)
@@ -588,7 +590,7 @@ extern "C" int drt_renderer_set_flags(drt_renderer* r, uint32_t flags)
 extern "C" int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads)
 {
 	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: null renderer");
-	if (variant < -1 || variant > 18 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
+	if (variant < -1 || variant > 23 || block_threads < 0 || block_threads > 256 || block_threads % 32) return fail(DRT_ERR_INVALID, "drt_renderer_set_tuning: bad value");
 	r->auto_variant = variant < 0;
 	r->variant = variant < 0 ? 4 : variant; r->block_threads = block_threads;
 	return DRT_OK;
@@ -710,6 +712,7 @@ extern "C" uint32_t drt_renderer_sample_count(const drt_renderer* r) { return r 
 extern "C" uint32_t drt_renderer_width(const drt_renderer* r) { return r ? r->width : 0; }
 extern "C" uint32_t drt_renderer_height(const drt_renderer* r) { return r ? r->height : 0; }
 extern "C" int drt_renderer_kernel_launches(const drt_renderer* r) { return r ? r->kernel_launches : 0; }
+extern "C" int drt_renderer_last_variant(const drt_renderer* r) { return r ? r->last_variant : -1; }
 
 static int make_render_params(drt_renderer* r, const drt_camera* cam, const drt_scene* scene, const drt_settings* settings, RenderParams& P)
 {
@@ -728,6 +731,7 @@ static int make_render_params(drt_renderer* r, const drt_camera* cam, const drt_
 	P.work_queue = r->work_queue.p;
 	P.tile_first = r->tile_first; P.tile_stride = r->tile_stride;
 	P.rg_overflow = r->rg_overflow.p;
+	P.pool_scratch = r->pool_scratch.p;
 	return DRT_OK;
 }
 
@@ -829,6 +833,19 @@ static int render_launch(drt_renderer* r, const drt_camera* cam, const drt_scene
 	P.n_samples = n;
 	P.total_samples = (float)(r->samples_done + n); // = the frame index the reference divides by (RenderKernel.cu:30)
 	LaunchConfig cfg = launch_config(r);
+	const bool pool_auto = cfg.auto_variant && cfg.variant == 4 && n >= DRT_POOL_MIN_SPP && scene->view.num_tris >= DRT_POOL_MIN_TRIS &&
+		scene->view.nodes_f32 != nullptr && !(r->flags & (DRT_FLAG_STATS | DRT_FLAG_EXTENDED_MATERIALS | DRT_FLAG_WATERTIGHT)) && P.shade.render_mode == 0;
+	if (cfg.variant == 22 || cfg.variant == 23 || pool_auto) { // (grown on demand, outside any timed launch: the pool colours of one launch)
+		const long long all_tiles = (long long)((r->width + 7) / 8) * ((r->height + 3) / 4);
+		const long long tiles = all_tiles > r->tile_first ? (all_tiles - r->tile_first + r->tile_stride - 1) / r->tile_stride : 0;
+		const size_t need = sample_pool_scratch_bytes(tiles, sample_pool_size(n, r->sched_bias[2]));
+		if (need > r->pool_scratch.n && !(pool_auto && need > DRT_POOL_MAX_SCRATCH_BYTES)) {
+			DRT_CUDA(cudaStreamSynchronize(r->stream));
+			DRT_CUDA(r->pool_scratch.alloc(need));
+		}
+		P.pool_scratch = r->pool_scratch.p;
+		cfg.pool_scratch_bytes = r->pool_scratch.n;
+	}
 	if (cfg.variant == 16 && !r->rg_overflow.p) { // (a one-off: entries beyond the shared-memory part of the regrouping kernel's stacks)
 		DRT_CUDA(r->rg_overflow.alloc(regroup_overflow_bytes(r->sm_count)));
 		P.rg_overflow = r->rg_overflow.p;
@@ -837,7 +854,7 @@ static int render_launch(drt_renderer* r, const drt_camera* cam, const drt_scene
 	const int candidate = autotune_pick(r, scene, P, probing);
 	if (candidate >= 0) autotune_apply(candidate, n, cfg);
 	DRT_CUDA(cudaEventRecord(r->ev0, r->stream));
-	DRT_CUDA(launch_render(P, cfg, r->stream, &r->kernel_launches));
+	DRT_CUDA(launch_render(P, cfg, r->stream, &r->kernel_launches, &r->last_variant));
 	DRT_CUDA(cudaEventRecord(r->ev1, r->stream));
 	*candidate_out = candidate; *probing_out = probing;
 	r->samples_done += n;

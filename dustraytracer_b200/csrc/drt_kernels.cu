@@ -88,6 +88,20 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 		V3 acc = mk3(0.f, 0.f, 0.f);
 		if (valid) { const float4 a4 = P.accum[p]; acc = mk3(a4.x, a4.y, a4.z); }
 		__shared__ alignas(16) uint8_t lut[DRT_PERMUTE_LUT_BYTES];
+		if (VARIANT == 22 || VARIANT == 23) {
+			// sample pool: the last tune.pool samples of the tile's pixels are handed out dynamically (render_warp_phased POOL)
+			__shared__ unsigned pool_counter[8];
+			__shared__ uint32_t pool_cold[4 * DRT_POOL_COLD_THREADS];
+			const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+			if (lane == 0) pool_counter[warp] = 0u;
+			__syncwarp();
+			SamplePool sp;
+			sp.counters = pool_counter;
+			sp.cold = pool_cold;
+			sp.warps_per_block = warps_per_block;
+			acc = render_warp_phased<STRICT, STATS, NODE_FMT_F32, VARIANT == 23, LaneStack, false, true>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st, lut, nullptr, sp);
+		}
+		else
 		if (VARIANT == 21) // variant 4 with the watertight TRI step (DRT_FLAG_WATERTIGHT; production arithmetic only)
 			acc = render_warp_phased<false, STATS, NODE_FMT_F32, false, LaneStack, true>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st, lut);
 		else
@@ -505,8 +519,9 @@ __global__ void __launch_bounds__(256) k_build(const BuildArrays A, const int* i
 }
 
 template <bool STRICT, bool STATS>
-cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s)
+cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* variant_out)
 {
+#define DRT_RAN(V) do { if (variant_out) *variant_out = (V); } while (0)
 	const int threads = cfg.block_threads > 0 ? cfg.block_threads : 128;
 	const int wpb = threads / 32;
 	const long long all_tiles = (long long)((P.width + 7) / 8) * ((P.height + 3) / 4);
@@ -517,10 +532,12 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	PhasedTuning tune;
 	tune.stick = cfg.sched_bias[0] > 0 ? cfg.sched_bias[0] : 6; // measured: room best at 8, dense_monkey at 4 (33 = never)
 	tune.refill = cfg.sched_bias[1] > 0 ? cfg.sched_bias[1] : (P.n_samples <= 1 ? 12 : (P.n_samples <= 4 ? 6 : 1));
+	tune.pool = 0;
 	// the phased kernels implement NORMALMODE; the debug views go through the reference-shaped loop
 	int variant = cfg.variant;
 	if (cfg.ext_materials && P.shade.render_mode == DRT_RENDER_NORMAL) {
 		k_render_ext<STRICT, STATS><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb);
+		DRT_RAN(-2);
 		return cudaGetLastError();
 	}
 	if (variant >= 2 && P.shade.render_mode != DRT_RENDER_NORMAL) variant = 1;
@@ -528,11 +545,12 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	// whole point is the reference's predicate, and only where the scene has vertex records and expanded nodes
 	if (cfg.watertight && !STRICT && variant >= 2 && P.scene.tris_v != nullptr && P.scene.nodes_f32 != nullptr && threads == 128) {
 		k_render<false, STATS, 21><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+		DRT_RAN(21);
 		return cudaGetLastError();
 	}
 	// variant 16: block-level regrouping (no statistics build of it: counted launches run the per-warp voting kernel)
 	if (variant == 16) {
-		if (!STATS && P.work_queue != nullptr && cfg.resident_sms > 0 && P.tile_stride > 0 && P.width < 65536 && P.height < 65536) return launch_regroup<STRICT>(P, cfg, s);
+		if (!STATS && P.work_queue != nullptr && cfg.resident_sms > 0 && P.tile_stride > 0 && P.width < 65536 && P.height < 65536) { DRT_RAN(16); return launch_regroup<STRICT>(P, cfg, s); }
 		variant = 4;
 	}
 	// variants 9 / 10: persistent warps with a pixel queue, for launches of few samples (the reference's interactive pattern is
@@ -558,6 +576,7 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 			if (q8) k_render_cold<STRICT, STATS, 4><<<(unsigned)qblocks, threads, 0, s>>>(P, cfg.rtl, tune);
 			else if (tri2) k_render_cold<STRICT, STATS, 6><<<(unsigned)qblocks, threads, 0, s>>>(P, cfg.rtl, tune);
 			else k_render_cold<STRICT, STATS, 3><<<(unsigned)qblocks, threads, 0, s>>>(P, cfg.rtl, tune);
+			DRT_RAN(q8 ? 10 : 9);
 			return cudaGetLastError();
 		}
 		else {
@@ -565,15 +584,34 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 			else if (variant == 12) k_render_cold<STRICT, STATS, 1><<<blocks, threads, 0, s>>>(P, cfg.rtl, tune);
 			else if (variant == 13) k_render_cold<STRICT, STATS, 2><<<blocks, threads, 0, s>>>(P, cfg.rtl, tune);
 			else k_render_cold<STRICT, STATS, 0><<<blocks, threads, 0, s>>>(P, cfg.rtl, tune);
+			DRT_RAN(variant);
 			return cudaGetLastError();
 		}
 	}
 	if (cfg.auto_variant && variant == 4 && P.scene.num_tris >= DRT_TRI2_MIN_TRIS) variant = 15;
+	// automatic selection: launches of DRT_POOL_MIN_SPP samples or more on scenes of DRT_POOL_MIN_TRIS triangles or more run the
+	// sample-pool form of the kernel (variants 22 / 23) when the renderer has provided the scratch array
+	if (cfg.auto_variant && (variant == 4 || variant == 15) && P.n_samples >= DRT_POOL_MIN_SPP && P.scene.num_tris >= DRT_POOL_MIN_TRIS &&
+		P.pool_scratch != nullptr) variant = variant == 4 ? 22 : 23;
 	if ((variant == 17 || variant == 18) && (P.scene.nodes_f32 == nullptr || threads != 128)) variant = variant == 17 ? 4 : 15; // (shared-memory stack: fp32 nodes, 128 threads)
+	if (variant == 22 || variant == 23) {
+		// sample pool: needs the scratch array (one float4 per pool sample of every owned tile), fp32 nodes, 128 threads
+		tune.pool = sample_pool_size(P.n_samples, cfg.sched_bias[2]);
+		const bool ok = tune.pool > 0 && P.scene.nodes_f32 != nullptr && threads == 128 && P.pool_scratch != nullptr && P.width < 65536 && P.height < 65536 &&
+			sample_pool_scratch_bytes(tiles, tune.pool) <= cfg.pool_scratch_bytes;
+		if (!ok) { variant = variant == 22 ? 4 : 15; tune.pool = 0; }
+		else {
+			if (variant == 22) k_render<STRICT, STATS, 22><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+			else k_render<STRICT, STATS, 23><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+			DRT_RAN(variant);
+			return cudaGetLastError();
+		}
+	}
 	if (variant == 15 && (P.scene.nodes_f32 == nullptr || threads > 128)) variant = 4; // (two-triangle TRI step: fp32 nodes, 128 threads)
 	if ((variant == 2 || (variant >= 4 && variant <= 6)) && P.scene.nodes_f32 == nullptr) variant = threads <= 128 ? 7 : 3;
 	if (variant >= 7 && threads > 128) variant = 3;
 	if (variant >= 4 && variant <= 6 && threads > 128) variant = 2;
+	DRT_RAN(variant);
 	if (variant == 17) k_render<STRICT, STATS, 17><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else if (variant == 18) k_render<STRICT, STATS, 18><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else
@@ -589,18 +627,33 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	else if (variant == 1) k_render<STRICT, STATS, 1><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else k_render<STRICT, STATS, 0><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	return cudaGetLastError();
+#undef DRT_RAN
 }
 
 } // namespace
 
+// R = pool samples per pixel: the pool has to cover the spread between a tile's fastest and slowest lane, ~1.1 sqrt(n) samples
+// (fit of the fixed-tile kernel's t(spp)); measured on room.glb (profiles/r02c_sample_pool.txt): 32 spp saturates at R = 8-9,
+// 256 spp at R = 24-32. At least half of the samples stay with their own pixel. override_r > 0 forces R (sweeps).
+int sample_pool_size(uint32_t n_samples, int override_r)
+{
+	if (n_samples < 2u) return 0;
+	int r = override_r > 0 ? override_r : (int)ceilf(1.5f * sqrtf((float)n_samples)) + 1;
+	if (r > 32 && override_r <= 0) r = 32;
+	if ((uint32_t)r > n_samples / 2u && override_r <= 0) r = (int)(n_samples / 2u);
+	if ((uint32_t)r > n_samples) r = (int)n_samples;
+	return r;
+}
+size_t sample_pool_scratch_bytes(long long tiles, int pool_r) { return (size_t)(tiles > 0 ? tiles : 0) * 32u * (size_t)(pool_r > 0 ? pool_r : 0) * sizeof(float4); }
+
 size_t regroup_overflow_bytes(int sms) { return (size_t)sms * DRT_RG_BLOCKS_PER_SM * DRT_RG_CTX * DRT_PSTACK * sizeof(uint2); }
 
-cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches)
+cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches, int* variant_out)
 {
 	if (launches) *launches += 1;
 	if (cfg.block_threads % 32 != 0 || cfg.block_threads > 256) return cudaErrorInvalidValue;
-	if (cfg.strict) return cfg.stats ? launch_render_v<true, true>(P, cfg, s) : launch_render_v<true, false>(P, cfg, s);
-	return cfg.stats ? launch_render_v<false, true>(P, cfg, s) : launch_render_v<false, false>(P, cfg, s);
+	if (cfg.strict) return cfg.stats ? launch_render_v<true, true>(P, cfg, s, variant_out) : launch_render_v<true, false>(P, cfg, s, variant_out);
+	return cfg.stats ? launch_render_v<false, true>(P, cfg, s, variant_out) : launch_render_v<false, false>(P, cfg, s, variant_out);
 }
 
 cudaError_t launch_trace_primary(const RenderParams& P, uint32_t frame_index, Hit* out_dev, const LaunchConfig& cfg, cudaStream_t s)

@@ -17,6 +17,22 @@ namespace drt {
 #define DRT_TRI2_MIN_TRIS 1024
 #endif
 
+// Automatic kernel selection: the sample-pool kernels (variants 22 / 23) replace variants 4 / 15 for launches of at least
+// DRT_POOL_MIN_SPP samples on scenes of at least DRT_POOL_MIN_TRIS triangles (measured, profiles/r02c_sample_pool.txt: room.glb
+// +3.5 % at 256 spp ... +16 % at 16 spp, dense_monkey / valorant_ghost / animemaid +5-9 % at 64 spp; the 34-triangle cornell_box,
+// whose samples are 1.2 rays long, -4.5 %).
+#ifndef DRT_POOL_MIN_SPP
+#define DRT_POOL_MIN_SPP 8
+#endif
+#ifndef DRT_POOL_MIN_TRIS
+#define DRT_POOL_MIN_TRIS 128
+#endif
+// Upper bound of the scratch array the renderer allocates for the pool on its own (pixels x R x 16 bytes; beyond it the
+// launch runs variants 4 / 15).
+#ifndef DRT_POOL_MAX_SCRATCH_BYTES
+#define DRT_POOL_MAX_SCRATCH_BYTES (4ull << 30)
+#endif
+
 struct LaunchConfig {
 	bool strict = false;  // DRT_FLAG_STRICT
 	bool rtl = false;     // DRT_FLAG_HOST_ARG_ORDER
@@ -28,14 +44,20 @@ struct LaunchConfig {
 	int sched_bias[3] = { 0, 0, 0 }; // phased kernels: [0] = sticky re-issue threshold (0 = default 6, 33 = never)
 	int block_threads = 0; // 0 = variant default
 	int resident_sms = 0;  // SM count of the device (grid of the persistent kernel)
+	size_t pool_scratch_bytes = 0; // capacity of RenderParams::pool_scratch (sample-pool kernel)
 };
 
+// Sample-pool kernel: pool samples per pixel for a launch of n samples (0: the launch is too short for a pool) and the scratch
+// bytes a launch over `tiles` 8x4 tiles needs.
+int sample_pool_size(uint32_t n_samples, int override_r);
+size_t sample_pool_scratch_bytes(long long tiles, int pool_r);
 // Bytes of the regrouping kernel's traversal-stack overflow area for a device of `sms` multiprocessors (RenderParams::rg_overflow).
 size_t regroup_overflow_bytes(int sms);
 cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s);
 cudaError_t launch_vertex_records(const drt_f4* tris, const float* pos, drt_f4* out, int n, cudaStream_t s);
 cudaError_t launch_expand_nodes(const WideNode* wide, drt_f4* out_f32, int n, cudaStream_t s);
-cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches);
+// variant_out (may be null): the kernel variant the launch ran after automatic selection and fall-backs (-2 = extended materials)
+cudaError_t launch_render(const RenderParams& P, const LaunchConfig& cfg, cudaStream_t s, int* launches, int* variant_out = nullptr);
 cudaError_t launch_trace_primary(const RenderParams& P, uint32_t frame_index, Hit* out_dev, const LaunchConfig& cfg, cudaStream_t s);
 cudaError_t launch_trace_rays(const SceneView& sc, const float* org_dev, const float* dir_dev, int n, bool anyhit, Hit* out_dev, const LaunchConfig& cfg, cudaStream_t s);
 cudaError_t launch_resolve(drt_f4* display, const drt_f4* accum, int n_pixels, float total_samples, cudaStream_t s);

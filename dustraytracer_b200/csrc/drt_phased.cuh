@@ -590,9 +590,9 @@ DRT_HD void path_begin_sample(const RenderParams& P, uint32_t x, uint32_t y, boo
 // SHADE step: consumes the finished ray of this lane. Returns false when the lane has no more work
 // (all samples of its pixel are accumulated); otherwise S.o / S.d hold the next ray to trace.
 // Block for block this is the body of render_pixel_flat() (drt_shade.cuh), i.e. RayGen.cuh:88-169.
+// shade_core: everything of the step up to the decision "this sample is complete" (returned); S.o / S.d hold the next ray otherwise.
 template <bool STRICT, bool STATS>
-DRT_HD bool shade_step(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, const Hit& hit, LanePath& S,
-	PathCounters& pc, TraceStats* st)
+DRT_HD bool shade_core(const RenderParams& P, bool rtl, const Hit& hit, LanePath& S, PathCounters& pc, TraceStats* st)
 {
 	typedef M<STRICT> m;
 	const SceneView& sc = P.scene;
@@ -643,7 +643,15 @@ DRT_HD bool shade_step(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, 
 		S.bounce++;
 		if (S.bounce > SP.bounce_limit) path_done = true;
 	}
-	if (path_done) {
+	return path_done;
+}
+
+template <bool STRICT, bool STATS>
+DRT_HD bool shade_step(const RenderParams& P, uint32_t x, uint32_t y, bool rtl, const Hit& hit, LanePath& S,
+	PathCounters& pc, TraceStats* st)
+{
+	typedef M<STRICT> m;
+	if (shade_core<STRICT, STATS>(P, rtl, hit, S, pc, st)) {
 		S.acc = m::add3(S.acc, post_process<STRICT>(P, S.light));
 		S.k++;
 		if (S.k >= P.n_samples) return false;
@@ -694,6 +702,7 @@ DRT_HD V3 render_pixel_steps(const RenderParams& P, uint32_t x, uint32_t y, bool
 struct PhasedTuning {
 	int stick;  // a step is re-issued without a full vote while at least this many lanes want it again (33 = never)
 	int refill; // pixel-queue kernel: idle lanes take new pixels once at least this many of them wait (1..32)
+	int pool;   // sample-pool kernel: the last `pool` samples of every pixel of a tile are handed out dynamically (0 = none)
 };
 
 // The permutation table, constant-initialised in device memory (2 KB, L2/L1 resident), and the per-block copy to
@@ -731,11 +740,44 @@ __device__ __forceinline__ void stack_bind(LaneStack&, uint32_t*) {}
 __device__ __forceinline__ void stack_bind(SharedLaneStack& K, uint32_t* words) { K.s = words + threadIdx.x; }
 
 // One warp: every lane owns one pixel (valid or not) for all samples of the launch.
-template <bool STRICT, bool STATS, int FMT, bool TRI2 = false, class STACK = LaneStack, bool WT = false>
+// POOL (sample pool): a warp of the fixed-tile kernel lives until its SLOWEST lane has finished; a lane's work is a sum of spp
+// random path lengths, so that wait grows like sqrt(spp): measured t(spp) = 0.481 spp + 0.525 sqrt(spp) ms on room.glb 1080p
+// (profiles/r02c_strided_tiles_and_spp_model.txt) -- 6 % of a 256-spp launch, 16 % of the 32-spp launches of 8 GPUs sharing a frame.
+// Here every lane renders only the first n - R samples of its own pixel; the last R samples of all 32 pixels of the tile
+// form a pool of 32 R (pixel, sample) items that the lanes take one at a time as they become free (one shared-memory atomic
+// per item), so fast lanes take more of them and the warp ends within about one sample of its average lane. Pool samples stay
+// in the warp's own tile (the rays stay coherent). Their colours go to a scratch array and every pixel adds its R pool
+// colours in sample order at the end: per pixel the same values are added in the same order as always (same bits).
+struct SamplePool {
+	unsigned* counters;  // shared memory, one word per warp of the block: next pool item
+	uint32_t* cold;      // shared memory, 4 words per thread ([word][thread], DRT_POOL_COLD_THREADS threads): the pixel's running sum
+	                     // and its coordinates -- touched once per sample, kept out of the registers of the NODE / TRI steps
+	int warps_per_block;
+};
+#define DRT_POOL_COLD_THREADS 128
+// (pointers and tile coordinates are recomputed where they are needed -- once per pool sample -- instead of being carried in
+// registers through the NODE / TRI steps: the kernel runs at its register limit)
+__device__ __forceinline__ float4* pool_scratch_of_warp(const RenderParams& P, const SamplePool& pool, uint32_t pool_r)
+{
+	return (float4*)P.pool_scratch + ((size_t)blockIdx.x * pool.warps_per_block + (threadIdx.x >> 5)) * 32u * (size_t)pool_r;
+}
+
+template <bool STRICT, bool STATS, int FMT, bool TRI2 = false, class STACK = LaneStack, bool WT = false, bool POOL = false>
 __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const PhasedTuning T, uint32_t x, uint32_t y, bool valid,
-	bool rtl, V3 acc, PathCounters& pc, TraceStats* st, uint8_t* lut, uint32_t* stack_words = nullptr)
+	bool rtl, V3 acc, PathCounters& pc, TraceStats* st, uint8_t* lut, uint32_t* stack_words = nullptr, SamplePool pool = SamplePool())
 {
 	const uint4 lut_part = permute_lut_load();
+#define DRT_POOL_R (POOL ? ((uint32_t)T.pool < P.n_samples ? (uint32_t)T.pool : P.n_samples) : 0u) /* R */
+#define DRT_POOL_OWN_END (P.n_samples - DRT_POOL_R)                                                 /* samples of the own pixel */
+	// POOL keeps the lane's own pixel and the pixel it is sampling in ONE register each (x | y << 16) and no item number: a lane is
+	// on its own pixel while S.k < DRT_POOL_OWN_END, and a pool item is (S.k - DRT_POOL_OWN_END) * 32 + position in the tile
+	uint32_t xy = x | (y << 16);
+	uint32_t* const cold = POOL ? pool.cold + threadIdx.x : nullptr;
+#define DRT_POOL_XY_OWN (cold[3 * DRT_POOL_COLD_THREADS])
+	if (POOL) {
+		cold[0] = __float_as_uint(acc.x); cold[DRT_POOL_COLD_THREADS] = __float_as_uint(acc.y); cold[2 * DRT_POOL_COLD_THREADS] = __float_as_uint(acc.z);
+		DRT_POOL_XY_OWN = xy;
+	}
 	LanePath S;
 	LaneTrav L;
 	STACK K;
@@ -750,8 +792,25 @@ __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const Ph
 	trav_begin(L, FLT_MAX);
 	R.oct_inv = 0u;
 	R.idnx = R.idny = R.idnz = R.bnx = R.bny = R.bnz = R.idfx = R.idfy = R.idfz = R.bfx = R.bfy = R.bfz = 0.f;
-	if (valid && P.n_samples > 0) {
-		path_begin_sample<STRICT>(P, x, y, rtl, S);
+	// POOL: the next pool item whose pixel lies inside the image; false when the pool is empty
+	// POOL: takes the next pool item whose pixel lies inside the image (xy, S.k = its pixel and sample); false when the pool is empty
+	auto pool_take = [&]() -> bool {
+		for (;;) {
+			const uint32_t item = atomicAdd(pool.counters + (threadIdx.x >> 5), 1u);
+			if (item >= 32u * DRT_POOL_R) return false;
+			const uint32_t lane = threadIdx.x & 31u, xy_own = DRT_POOL_XY_OWN;
+			const uint32_t px = (xy_own & 0xffffu) - (lane & 7u) + (item & 7u), py = (xy_own >> 16) - (lane >> 3) + ((item >> 3) & 3u);
+			if (px < (uint32_t)P.width && py < (uint32_t)P.height) { xy = px | (py << 16); S.k = DRT_POOL_OWN_END + (item >> 5); return true; }
+		}
+	};
+	bool start = valid && P.n_samples > 0; // this lane has a sample to start
+	if (POOL) {
+		// (a lane without a pixel of its own -- ragged image edge -- still works on the pool of its tile)
+		const bool tile_live = __ballot_sync(0xffffffffu, valid) != 0u && P.n_samples > 0;
+		start = tile_live && ((valid && DRT_POOL_OWN_END > 0u) || pool_take());
+	}
+	if (start) {
+		path_begin_sample<STRICT>(P, POOL ? (xy & 0xffffu) : x, POOL ? (xy >> 16) : y, rtl, S);
 		ray_box_setup(S.o, S.d, R);
 		phase = first_phase;
 	}
@@ -779,7 +838,29 @@ __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const Ph
 					else phase = trav_advance(L, K);
 				}
 				else {
-					if (!shade_step<STRICT, STATS>(P, x, y, rtl, L.hit, S, pc, st)) phase = PH_DONE;
+					bool more;
+					if (POOL) {
+						more = true;
+						if (shade_core<STRICT, STATS>(P, rtl, L.hit, S, pc, st)) { // the sample is complete
+							const V3 c = post_process<STRICT>(P, S.light);
+							bool take = true;
+							if (S.k < DRT_POOL_OWN_END) { // a sample of the own pixel
+								const V3 a = M<STRICT>::add3(mk3(__uint_as_float(cold[0]), __uint_as_float(cold[DRT_POOL_COLD_THREADS]), __uint_as_float(cold[2 * DRT_POOL_COLD_THREADS])), c);
+								cold[0] = __float_as_uint(a.x); cold[DRT_POOL_COLD_THREADS] = __float_as_uint(a.y); cold[2 * DRT_POOL_COLD_THREADS] = __float_as_uint(a.z);
+								S.k++;
+								take = S.k >= DRT_POOL_OWN_END; // (xy is still the own pixel)
+							}
+							else { // a pool sample: its colour goes to [sample of the pool][position of its pixel in the tile]
+								const uint32_t lane = threadIdx.x & 31u, xy_own = DRT_POOL_XY_OWN;
+								const uint32_t pos = ((xy & 0xffffu) - ((xy_own & 0xffffu) - (lane & 7u))) + 8u * ((xy >> 16) - ((xy_own >> 16) - (lane >> 3)));
+								pool_scratch_of_warp(P, pool, DRT_POOL_R)[(S.k - DRT_POOL_OWN_END) * 32u + pos] = make_float4(c.x, c.y, c.z, 0.f);
+							}
+							if (take) more = pool_take();
+							if (more) path_begin_sample<STRICT>(P, xy & 0xffffu, xy >> 16, rtl, S);
+						}
+					}
+					else more = shade_step<STRICT, STATS>(P, x, y, rtl, L.hit, S, pc, st);
+					if (!more) phase = PH_DONE;
 					else {
 						ray_box_setup(S.o, S.d, R);
 						trav_begin(L, FLT_MAX);
@@ -789,6 +870,21 @@ __device__ __forceinline__ V3 render_warp_phased(const RenderParams& P, const Ph
 			}
 		} while (__popc(__ballot_sync(0xffffffffu, phase == pick)) >= T.stick);
 	}
+	if (POOL) S.acc = mk3(__uint_as_float(cold[0]), __uint_as_float(cold[DRT_POOL_COLD_THREADS]), __uint_as_float(cold[2 * DRT_POOL_COLD_THREADS]));
+	if (POOL && DRT_POOL_R > 0u) {
+		// every pool colour of the tile is in the scratch array: each pixel adds its own in sample order (RenderKernel.cu:29)
+		__syncwarp();
+		if (valid) {
+			const float4* sc = pool_scratch_of_warp(P, pool, DRT_POOL_R) + (threadIdx.x & 31u);
+			for (uint32_t j = 0; j < DRT_POOL_R; j++) {
+				const float4 c = sc[j * 32u];
+				S.acc = M<STRICT>::add3(S.acc, mk3(c.x, c.y, c.z));
+			}
+		}
+	}
+#undef DRT_POOL_R
+#undef DRT_POOL_OWN_END
+#undef DRT_POOL_XY_OWN
 	return S.acc;
 }
 

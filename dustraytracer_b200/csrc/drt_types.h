@@ -105,6 +105,7 @@ struct RenderParams {
 	Counters* counters;
 	unsigned* work_queue;   // 2 words, zero between launches: next tile, warps that have left (pixel-queue kernel)
 	uint32_t tile_first, tile_stride; // image-tile sharding: this launch owns the 8x4 tiles first, first+stride, ... (row-major tile index)
+	void* pool_scratch;     // sample-pool kernel (variants 22 / 23): pool colours, float4 x 32 x R per owned tile (may be null)
 	void* rg_overflow;      // regrouping kernel (variant 16): traversal-stack entries beyond the shared-memory ones, DRT_PSTACK x 8 bytes per resident context (may be null)
 };
 

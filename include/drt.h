@@ -168,10 +168,15 @@ int drt_renderer_set_flags(drt_renderer* r, uint32_t flags);
  * NODE/TRI/SHADE steps, 6 blocks/SM (expanded fp32 nodes when the scene has them), 2 = the same without the register cap,
  * 3 / 7 / 8 = compressed nodes, 0 = flat per-thread state machine, 1 = per-sample bounce loop, 11-14 = variant 4 / 7 with
  * the SHADE-only lane state in shared memory (8 / 7 / 6 blocks per SM; 14 = compressed nodes), 9 / 10 = their persistent
- * pixel-queue form (fp32 / compressed nodes). block_threads = 0 (default 128) or a multiple of 32 up to 256. */
+ * pixel-queue form (fp32 / compressed nodes), 16 = block-level regrouping of path contexts in shared memory (measured alternative),
+ * 17 / 18 = variants 4 / 15 with a shared-memory traversal stack (measured alternative), 22 / 23 = variants 4 / 15 with a SAMPLE POOL:
+ * the last R of a pixel's samples are handed out dynamically inside the warp's tile, which removes the wait for the slowest lane
+ * (what automatic selection runs for launches of >= 8 samples on scenes of >= 128 triangles; same bits as every other variant).
+ * block_threads = 0 (default 128) or a multiple of 32 up to 256. */
 int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_threads);
 void drt_renderer_destroy(drt_renderer* r);
 int drt_renderer_kernel_launches(const drt_renderer* r); /* kernels launched by this renderer so far */
+int drt_renderer_last_variant(const drt_renderer* r);    /* kernel variant the last render launch ran (automatic selection resolved) */
 /* Checkpoint / resume: restore accumulation sums (3 floats / pixel) and the number of samples they hold. */
 int drt_renderer_upload_accum(drt_renderer* r, const float* rgb32f, size_t bytes, uint32_t samples_done);
 /* Sample-range sharding across GPUs: this renderer renders frame indices first, first+stride, ... (default 1, 1). */

@@ -92,7 +92,7 @@ def test_primary_hits_bit_exact(drt, name):
     assert np.all(np.abs(sub[same] - g["tuv_stride4"][0][same]) <= 1e-4 * g["tuv_stride4"][0][same])
 
 
-@pytest.mark.parametrize("variant", [4, 2, 3, 0, 1, 9, 10, 11, 14, 15, 16, 17])
+@pytest.mark.parametrize("variant", [4, 2, 3, 0, 1, 9, 10, 11, 14, 15, 16, 17, 22, 23])
 @pytest.mark.parametrize("name", SCENES)
 def test_accumulated_image_bit_exact(drt, name, variant):
     g = np.load(os.path.join(GOLDEN, "scene_%s.npz" % name))
@@ -169,7 +169,7 @@ def test_pixel_queue_kernel_matches_fixed_pixel_kernel(drt, name, size):
     for batches in ([1, 1, 1, 1, 1], [3, 2], [5]):
         a4, d4, c4 = run(4, batches)
         a3, d3, c3 = run(3, batches)
-        for variant in (9, 10, 11, 12, 13, 14, 15, 17, 18):
+        for variant in (9, 10, 11, 12, 13, 14, 15, 17, 18, 22, 23):
             a, d, c = run(variant, batches)
             ref_a, ref_d, ref_c = (a3, d3, c3) if variant in (10, 14) else (a4, d4, c4)
             assert np.array_equal(bits(a), bits(ref_a)) and np.array_equal(bits(d), bits(ref_d)), (variant, batches)
@@ -201,7 +201,7 @@ def test_launch_autotuner_is_invisible_in_the_results(drt, name):
     assert np.array_equal(bits(a), bits(b)) and ca == cb and la == lb
 
 
-@pytest.mark.parametrize("variant", [4, 3, 9, 10, 0, 16])
+@pytest.mark.parametrize("variant", [4, 3, 9, 10, 0, 16, 22])
 def test_tile_sharding_is_a_partition_of_the_image(drt, variant):
     """drt_renderer_set_tile_schedule: three renderers own the 8x4 tiles 0,3,6.. / 1,4,7.. / 2,5,8.. of a ragged image;
     each touches exactly the pixels of tile_owner_mask, and the SUM of their accumulation buffers has the bits of the

@@ -409,3 +409,48 @@ def test_watertight_mode_closes_the_cracks_of_moller_trumbore(drt):
     # the pixel-queue and regrouping kernels do not have the watertight step: the flag wins over an explicit variant
     a9, c9 = render(WT, 9)
     assert np.array_equal(bits(a9), bits(a1)) and c9 == c1
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the sample-pool kernels (variants 22 / 23; what automatic selection runs for launches of >= 8 samples)
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,size", [("room", (101, 67)), ("animemaid", (37, 5)), ("dense_monkey", (250, 131)), ("cornell_box", (9, 4))])
+def test_sample_pool_kernel_gives_the_bits_of_the_fixed_tile_kernel(drt, name, size):
+    """The last R samples of every pixel are rendered by whichever lane of the tile is free and added in sample order at the end:
+    ragged images (lanes without a pixel of their own still work on the pool), launches of 2 .. 70 samples (R from 1 to 14, own
+    part from half of the samples to most of them), several launches in a row, sample-range and tile schedules -- accumulation
+    buffers, display buffers and ray counters must have the bits of the fixed-tile kernel, in parity AND in production arithmetic
+    (the per-sample code is the same in both kernels). A renderer left on automatic selection must pick the pool kernel by itself."""
+    scene = gpu_scene(drt, name)
+    cam = drt.Camera()
+    st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=4, max_samples=100000)
+
+    def run(variant, batches, flags, sched=None):
+        r = drt.Renderer(flags=flags)
+        r.set_tuning(variant, 0)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(*size)
+        if sched == "frames":
+            r.set_frame_schedule(3, 4)
+        if sched == "tiles":
+            r.set_tile_schedule(1, 3)
+        ran = []
+        for b in batches:
+            r.Render(cam, scene, b)
+            ran.append(r.last_variant())
+        return r.readback(drt.DRT_ACCUM_RGB32F), r.readback(drt.DRT_RGBA32F), r.counters(), ran
+
+    big = scene.stats()["triangles"] >= 1024
+    base, pool = (15, 23) if big else (4, 22)
+    for flags in (STRICT, 0):
+        for batches, sched in (([2, 3, 9], None), ([37], None), ([70], None), ([16, 16], "frames"), ([24], "tiles")):
+            a0, d0, c0, _ = run(base, batches, flags, sched)
+            a1, d1, c1, ran = run(pool, batches, flags, sched)
+            assert ran == [pool] * len(batches), ran
+            assert np.array_equal(bits(a1), bits(a0)) and np.array_equal(bits(d1), bits(d0)), (flags, batches, sched)
+            assert c1 == c0, (flags, batches, sched)
+    a0, _, c0, _ = run(base, [40], 0)
+    a2, _, c2, ran = run(-1, [40], 0)
+    wanted = pool if scene.stats()["triangles"] >= 128 else base
+    assert ran == [wanted], ran
+    assert np.array_equal(bits(a2), bits(a0)) and c2 == c0
