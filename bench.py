@@ -633,7 +633,8 @@ def ncu_capture_summary():
     if "dram__bytes_read.sum" in vals and "dram__bytes_write.sum" in vals:
         out["traffic"] = sum(vals[k][0] * scale.get(vals[k][1], 1.0) for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
         out["traffic_note"] = ("bytes per launch, dram read+write of one k_render launch under ncu (%s-spp launch; "
-                               "a launch touches each frame-buffer pixel once whatever its sample count)" % spp)
+                               "the frame buffer is touched once per pixel whatever the sample count; with the sample-pool kernel the rest "
+                               "is the pool's colour scratch, 16 B per pooled sample written once and read back through L2)" % spp)
     get = lambda k: vals[k][0] if k in vals else None
     out["thread_inst"] = get("smsp__thread_inst_executed.sum")
     out["warp_inst"] = get("smsp__inst_executed.sum")
