@@ -46,7 +46,7 @@ class drt_scene_stats(ctypes.Structure):
     _fields_ = [(n, ctypes.c_uint64) for n in
                 ("triangles", "materials", "textures", "meshes", "wide_nodes", "bvh2_nodes", "bvh_levels", "device_bytes")] + \
                [("build_ms", ctypes.c_double), ("load_ms", ctypes.c_double)] + \
-               [(n, ctypes.c_uint64) for n in ("alpha_tris", "alpha_opaque", "alpha_hidden")]
+               [(n, ctypes.c_uint64) for n in ("alpha_tris", "alpha_opaque", "alpha_hidden", "build_launches")]
 
 
 class drt_hit(ctypes.Structure):

@@ -112,9 +112,10 @@ class Scene:
         h, w, c = px.shape
         check(_lib.lib().drt_scene_add_texture(self._h, w, h, c, px.ctypes.data))
 
-    def build_bvh(self, device=0, bin_count=8, leaf_target=20, classify_alpha=True):
+    def build_bvh(self, device=0, bin_count=8, leaf_target=20, classify_alpha=True, single_launch=True):
+        """single_launch=False forces the level-synchronous multi-launch builder also for small scenes (same tree; A/B)."""
         p = drt_bvh_params(bin_count=bin_count, leaf_target=leaf_target)
-        p.reserved[0] = 0 if classify_alpha else 1
+        p.reserved[0] = (0 if classify_alpha else 1) | (0 if single_launch else 2)
         check(_lib.lib().drt_scene_build_bvh(self._h, ctypes.byref(p), device))
 
     def stats(self):

@@ -326,6 +326,7 @@ int drt_decode_image(const uint8_t* data, size_t len, int32_t* width, int32_t* h
 extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* params_or_null, int device)
 {
 	const bool classify_alpha = !(params_or_null && (params_or_null->reserved[0] & 1));
+	const bool single_launch_build = !(params_or_null && (params_or_null->reserved[0] & 2)); // bit 1: force the level-synchronous build
 	if (!scene) return fail(DRT_ERR_INVALID, "drt_scene_build_bvh: null scene");
 	int ndev = 0;
 	DRT_CUDA(cudaGetDeviceCount(&ndev));
@@ -417,6 +418,7 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* param
 	DevBuf<WideNode> wide_tmp;
 	BuildResult res;
 	double build_ms = 0.0;
+	int build_launches = 0;
 	if (n > 0) {
 		DRT_CUDA(d_pos.alloc(9 * n)); DRT_CUDA(d_uv.alloc(6 * n)); DRT_CUDA(d_fn.alloc(3 * n)); DRT_CUDA(d_mat.alloc(n));
 		DRT_CUDA(tri_lo.alloc(n)); DRT_CUDA(tri_hi.alloc(n));
@@ -443,7 +445,17 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* param
 		cudaEvent_t e0, e1;
 		DRT_CUDA(cudaEventCreate(&e0)); DRT_CUDA(cudaEventCreate(&e1));
 		DRT_CUDA(cudaEventRecord(e0, stream));
-		int rc = run_build(ex, A, res);
+		int rc = 0;
+		if (single_launch_build && n <= (size_t)DRT_BUILD_SMALL_MAX_TRIS) {
+			// small scene: the whole level loop in one launch of one block (k_build_small), one read-back at the end
+			DevBuf<int> d_res;
+			int h_res[6] = { 0, 0, 0, 0, 0, 0 };
+			rc = ex.check(d_res.alloc(6)) || ex.check(launch_build_small(A, d_res.p, stream)) ||
+				ex.check(cudaMemcpyAsync(h_res, d_res.p, sizeof(h_res), cudaMemcpyDeviceToHost, stream)) || ex.check(cudaStreamSynchronize(stream));
+			ex.launches = 1;
+			res.bvh2_nodes = h_res[0]; res.wide_nodes = h_res[1]; res.levels = h_res[2]; res.wide_levels = h_res[3]; res.tris_emitted = h_res[4];
+		}
+		else rc = run_build(ex, A, res);
 		cudaEventRecord(e1, stream);
 		cudaError_t se = cudaStreamSynchronize(stream);
 		float ms = 0.f;
@@ -454,6 +466,7 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* param
 			return fail(DRT_ERR_CUDA, std::string("BVH build failed: ") + cudaGetErrorString(ex.last != cudaSuccess ? ex.last : se));
 		}
 		build_ms = ms;
+		build_launches = ex.launches;
 		if (res.tris_emitted != (int)n) return fail(DRT_ERR_CUDA, "BVH build emitted " + std::to_string(res.tris_emitted) + " of " + std::to_string(n) + " triangles");
 		// The render kernels keep DRT_PSTACK traversal-stack entries per lane and push at most one entry (the rest of a node group)
 		// per level of the wide tree: a tree deeper than that could lose subtrees, so it is refused here rather than rendered wrong.
@@ -489,6 +502,7 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* param
 	scene->stats.bvh2_nodes = (uint64_t)res.bvh2_nodes;
 	scene->stats.bvh_levels = (uint64_t)res.levels;
 	scene->stats.build_ms = build_ms;
+	scene->stats.build_launches = (uint64_t)build_launches;
 	scene->stats.device_bytes = scene->nodes.bytes() + scene->nodes_f32.bytes() + scene->tris.bytes() + scene->tris_v.bytes() + scene->shade.bytes() + scene->materials.bytes()
 		+ scene->texdesc.bytes() + scene->texels.bytes();
 	scene->built = true;

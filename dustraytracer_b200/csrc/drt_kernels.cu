@@ -718,6 +718,75 @@ cudaError_t launch_expand_nodes(const WideNode* wide, drt_f4* out, int n, cudaSt
 	return cudaGetLastError();
 }
 
+// The whole build of a SMALL scene in ONE launch (one block): the level loop of run_build (drt_build_driver.h) with block
+// barriers where the host loop has kernel boundaries and the BuildState words read back through shared memory instead of a
+// host round trip per level. Same per-index passes, hence the same tree; the level-synchronous path spends ~60 launches and a
+// dozen host read-backs on a 330-triangle scene (launch-latency bound: 0.9 ms), this one is bound by the block's own work.
+// result[0..5] = bvh2 nodes, wide nodes, levels, wide levels, triangles emitted, 1 if the final index array is A.idx_out.
+__global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(const BuildArrays A0, int* result)
+{
+	__shared__ int s_count[2];
+	BuildArrays A = A0;
+	const int tid = (int)threadIdx.x, nt = (int)blockDim.x, n = A.n;
+	if (tid == 0) {
+		init_node(&A.nodes[0], 0, n);
+		BuildSplit rs;
+		rs.axis = -1; rs.split_bin = 0; rs.n_left = 0; rs.bin_slot = n > DRT_SMALL_NODE ? 0 : -1;
+		A.splits[0] = rs;
+		A.wide_src[0] = 0;
+		BuildState st;
+		st.node_count = 1; st.wide_count = 1; st.tri_cursor = 0; st.bin_slots = n > DRT_SMALL_NODE ? 1 : 0;
+		*A.state = st;
+	}
+	__syncthreads();
+	for (int i = tid; i < n; i += nt) prim_bounds(A, i);
+	__syncthreads();
+	int level_start = 0, level_end = 1, level = 0, slot_base = 0, slot_end = n > DRT_SMALL_NODE ? 1 : 0, swapped = 0;
+	while (level_end > level_start) {
+		A.level_start = level_start; A.level_end = level_end; A.level = level; A.bin_slot_base = slot_base;
+		const int bin_words = (slot_end - slot_base) * 3 * DRT_BINS * DRT_BIN_WORDS;
+		if (bin_words > 0) {
+			for (int j = tid; j < bin_words; j += nt) init_bin_word(A, j, bin_words);
+			__syncthreads();
+			for (int i = tid; i < n; i += nt) bin_prim(A, i);
+			__syncthreads();
+		}
+		for (int j = tid; j < level_end - level_start; j += nt) split_node(A, j);
+		__syncthreads();
+		for (int i = tid; i < n; i += nt) partition_prim(A, i);
+		__syncthreads();
+		if (tid == 0) { s_count[0] = A.state->node_count; s_count[1] = A.state->bin_slots; }
+		__syncthreads();
+		int* t = A.idx_in; A.idx_in = A.idx_out; A.idx_out = t;
+		t = A.pnode_in; A.pnode_in = A.pnode_out; A.pnode_out = t;
+		swapped ^= 1;
+		level_start = level_end; level_end = s_count[0];
+		slot_base = slot_end; slot_end = s_count[1];
+		level++;
+		__syncthreads(); // s_count is rewritten at the end of the next level
+	}
+	const int bvh2_nodes = level_end;
+	int ws = 0, we = 1, wl = 0;
+	while (we > ws) {
+		for (int j = tid; j < we - ws; j += nt) collapse_node(A, A.idx_in, ws, we, j);
+		__syncthreads();
+		if (tid == 0) s_count[0] = A.state->wide_count;
+		__syncthreads();
+		ws = we; we = s_count[0]; wl++;
+		__syncthreads();
+	}
+	if (tid == 0) {
+		result[0] = bvh2_nodes; result[1] = we; result[2] = level; result[3] = wl; result[4] = A.state->tri_cursor; result[5] = swapped;
+	}
+}
+
+cudaError_t launch_build_small(const BuildArrays& A, int* result, cudaStream_t s)
+{
+	if (A.n <= 0) return cudaErrorInvalidValue;
+	k_build_small<<<1, DRT_BUILD_SMALL_THREADS, 0, s>>>(A, result);
+	return cudaGetLastError();
+}
+
 cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s)
 {
 	if (n <= 0) return cudaSuccess;

@@ -54,6 +54,14 @@ size_t sample_pool_scratch_bytes(long long tiles, int pool_r);
 // Bytes of the regrouping kernel's traversal-stack overflow area for a device of `sms` multiprocessors (RenderParams::rg_overflow).
 size_t regroup_overflow_bytes(int sms);
 cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s);
+// Single-launch build for small scenes (k_build_small: one block runs the whole level loop). `result` = 6 device ints:
+// bvh2 nodes, wide nodes, levels, wide levels, triangles emitted, 1 if the final index array is A.idx_out.
+#define DRT_BUILD_SMALL_THREADS 1024
+#ifndef DRT_BUILD_SMALL_MAX_TRIS
+#define DRT_BUILD_SMALL_MAX_TRIS 2048
+#endif
+cudaError_t launch_build_small(const BuildArrays& A, int* result, cudaStream_t s);
+
 cudaError_t launch_vertex_records(const drt_f4* tris, const float* pos, drt_f4* out, int n, cudaStream_t s);
 cudaError_t launch_expand_nodes(const WideNode* wide, drt_f4* out_f32, int n, cudaStream_t s);
 // variant_out (may be null): the kernel variant the launch ran after automatic selection and fall-backs (-2 = extended materials)

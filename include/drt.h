@@ -77,7 +77,9 @@ typedef struct drt_material {
 typedef struct drt_bvh_params {
 	int32_t bin_count;   /* informational: the GPU builder uses 16 bins (8 for small nodes); ref m_BinCount = 8 */
 	int32_t leaf_target; /* informational: wide-node leaf slots hold <= 3 triangles; ref m_TargetLeafPrimitivesCount */
-	int32_t reserved[6]; /* reserved[0] bit 0: disable the opacity classification of alpha-tested triangles (A/B checks) */
+	int32_t reserved[6]; /* reserved[0] bit 0: disable the opacity classification of alpha-tested triangles (A/B checks);
+	                        bit 1: build scenes of <= 2048 triangles with the level-synchronous multi-launch builder too instead
+	                        of the single-launch one (same tree; A/B checks) */
 } drt_bvh_params;
 
 typedef struct drt_scene_stats {
@@ -89,6 +91,7 @@ typedef struct drt_scene_stats {
 	/* alpha-tested triangles (albedo texture with 4 components, AnyHit.cuh:17), and how many of them the exact host-side
 	 * opacity classification proved always-opaque (test skipped) / never-hittable (collapsed); set by drt_scene_build_bvh */
 	uint64_t alpha_tris, alpha_opaque, alpha_hidden;
+	uint64_t build_launches; /* kernel launches of the last build: 1 for scenes of <= 2048 triangles (single-launch builder) */
 } drt_scene_stats;
 
 typedef struct drt_hit {
