@@ -783,7 +783,13 @@ __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(cons
 cudaError_t launch_build_small(const BuildArrays& A, int* result, cudaStream_t s)
 {
 	if (A.n <= 0) return cudaErrorInvalidValue;
-	k_build_small<<<1, DRT_BUILD_SMALL_THREADS, 0, s>>>(A, result);
+	// one thread per primitive up to the block limit (fewer threads = cheaper barriers; the passes are strided loops)
+	int threads = ((A.n + 31) / 32) * 32;
+	if (threads < 64) threads = 64;
+	if (threads > DRT_BUILD_SMALL_THREADS) threads = DRT_BUILD_SMALL_THREADS;
+	static const char* env = getenv("DRT_BUILD_SMALL_BLOCK"); // measurement override
+	if (env && atoi(env) >= 32 && atoi(env) <= DRT_BUILD_SMALL_THREADS) threads = (atoi(env) / 32) * 32;
+	k_build_small<<<1, threads, 0, s>>>(A, result);
 	return cudaGetLastError();
 }
 
