@@ -495,6 +495,35 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(rays2, op=dist.ReduceOp.SUM)
     e2e_rays = float(rays2[0])
 
+    # ---- N > 1: where the step goes (untimed extra steps; CUDA events on the launching stream around each part) ----
+    breakdown = None
+    if world > 1 and not p2p:
+        parts = []
+        for _ in range(5):
+            r.resetAccumulationBuffer()
+            barrier()
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            e[0].record(stream)
+            r.Render(cam, scene, rank_spp)
+            e[1].record(stream)
+            dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM)
+            e[2].record(stream)
+            if rank == 0:
+                r.resolve(frame_spp)
+            e[3].record(stream)
+            torch.cuda.synchronize(dev)
+            parts.append([e[i].elapsed_time(e[i + 1]) for i in range(3)])
+        r.counters(reset=True)
+        best = torch.tensor([min(p[i] for p in parts) for i in range(3)], dtype=torch.float64, device=dev)
+        worst = best.clone()
+        dist.all_reduce(worst[0:1], op=dist.ReduceOp.MAX)   # the slowest rank's launch is what the reduce waits for
+        if rank == 0:
+            breakdown = {"render_ms_slowest_rank": round(float(worst[0]), 4), "render_ms_rank0": round(float(best[0]), 4),
+                         "reduce_ms_rank0": round(float(best[1]), 4), "resolve_ms_rank0": round(float(best[2]), 4),
+                         "reduce_bytes": int(acc_t.numel() * 4),
+                         "note": "best of 5 untimed steps started from a barrier; reduce = ncclReduce of the W*H float4 sums to rank 0 as seen by rank 0 "
+                                 "(includes waiting for the slowest rank's launch); ideal render = one-GPU step / N"}
+
     if rank == 0:
         # ---- traversal statistics for the algorithmic-bytes term (untimed, small sample) ----
         rs = drt.Renderer(device=local_rank, flags=drt.DRT_FLAG_STATS)
@@ -595,6 +624,8 @@ def run_ours(args, rank, world, local_rank):
             "reference_cuda_on_this_gpu": refcuda,
             "rays_per_step": total_rays / args.steps, "wall_s_timed_region": t_wall,
         }
+        if breakdown:
+            line["step_breakdown"] = breakdown
         emit_json_line(line)
     if world > 1:
         dist.barrier()
