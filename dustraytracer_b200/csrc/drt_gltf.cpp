@@ -258,6 +258,9 @@ int load_gltf(const char* path, HostScene& out, std::string& err, unsigned flags
 			const size_t buf_len = blen[iv.buffer];
 			const size_t i_begin = iv.offset / 2, i_end = (iv.length + iv.offset) / 2;
 			const size_t o_pos = views[v_pos].offset, o_nrm = views[v_nrm].offset, o_uv = views[v_uv].offset;
+			// the reference reads every attribute from the INDEX accessor's buffer (Scene.cu:150-170); a view of another, longer
+			// buffer can start beyond this one's end, and `buf_len - o_*` below would wrap
+			if (o_pos > buf_len || o_nrm > buf_len || o_uv > buf_len) { err = "attribute bufferView starts beyond the index accessor's buffer"; return DRT_ERR_FORMAT; }
 			const size_t n_idx = i_end - i_begin;
 			size_t n_tri = n_idx / 3;
 			if (idx_count_accessor / 3 < n_tri) n_tri = idx_count_accessor / 3; // keep material/triangle arrays consistent

@@ -351,6 +351,43 @@ def test_crafted_byte_ranges_are_rejected_not_wrapped(tmp_path):
         assert e.value.code == -3, (key, val, str(e.value))
 
 
+def test_attribute_view_of_a_longer_second_buffer_cannot_index_past_the_first(tmp_path):
+    """The reference-compatible loader reads all attributes from the index accessor's buffer (the reference's quirk). A POSITION view
+    that is valid in a SECOND, longer buffer but starts beyond the end of the first must be refused there (the remaining-length
+    subtraction would wrap and the copy would read far out of bounds); the robust loader follows the accessor's own buffer."""
+    import base64
+    g = Glb()
+    ia = g.accessor(np.array([0, 1, 2], np.uint16))
+    na = g.accessor(np.array([[0, 0, 1]] * 3, np.float32))
+    ta = g.accessor(np.zeros((3, 2), np.float32))
+    second = bytearray(b"\0" * 8192)
+    tri = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    second[8000:8036] = tri.tobytes()
+    g.j["bufferViews"].append({"buffer": 1, "byteOffset": 8000, "byteLength": 36})
+    g.j["accessors"].append({"bufferView": len(g.j["bufferViews"]) - 1, "componentType": 5126, "count": 3, "type": "VEC3"})
+    pa = len(g.j["accessors"]) - 1
+    g.j["meshes"] = [{"primitives": [{"attributes": {"POSITION": pa, "NORMAL": na, "TEXCOORD_0": ta}, "indices": ia}]}]
+    g.j["nodes"] = [{"mesh": 0}]
+    path = str(tmp_path / "two_buffers.glb")
+    g.write(path)
+    # Glb.write emits one buffer: append the second as a data URI
+    raw = open(path, "rb").read()
+    jlen = struct.unpack_from("<I", raw, 12)[0]
+    j = json.loads(raw[20:20 + jlen])
+    j["buffers"].append({"byteLength": len(second), "uri": "data:application/octet-stream;base64," + base64.b64encode(bytes(second)).decode()})
+    js = json.dumps(j).encode()
+    js += b" " * ((4 - len(js) % 4) % 4)
+    rest = raw[20 + jlen:]
+    with open(path, "wb") as f:
+        f.write(struct.pack("<III", 0x46546C67, 2, 20 + len(js) + len(rest)) + struct.pack("<II", len(js), 0x4E4F534A) + js + rest)
+    with pytest.raises(drt.DrtError) as e:
+        load(path, robust=False)
+    assert e.value.code == -3 and "beyond" in str(e.value)
+    s = load(path, robust=True)
+    assert s.stats()["triangles"] == 1
+    assert np.array_equal(soup_of(s)[0].reshape(3, 3), tri)
+
+
 @pytest.mark.gpu
 def test_robust_scene_renders_like_the_same_soup_given_directly(tmp_path):
     """A transformed, strided, u32-indexed file loaded with DRT_LOAD_ROBUST traces exactly like the world-space
