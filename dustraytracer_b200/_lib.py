@@ -3,7 +3,7 @@ import ctypes
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libdrt.so")
+LIB_PATH = os.environ.get("DRT_LIB_PATH") or os.path.join(_PKG, "libdrt.so")  # (DRT_LIB_PATH: A/B measurement builds only)
 
 
 class drt_camera(ctypes.Structure):

@@ -16,10 +16,16 @@
 
 namespace drt {
 
+#ifndef DRT_BINS
 #define DRT_BINS 16          // SAH bins per axis for large nodes
+#endif
 #define DRT_SMALL_NODE 32    // nodes with <= this many primitives are split by their own thread
-#define DRT_SMALL_BINS 8
-#define DRT_LEAF_MAX 3       // triangles per leaf slot (unary-coded in 3 bits of WideNode::meta)
+#ifndef DRT_SMALL_BINS
+#define DRT_SMALL_BINS 16    // (<= DRT_BINS) bins of a small node's own sweep; 8 -> 16 in round 2: +1 ... +2.7 % on the scenes of > 6000 triangles (profiles/r02c_tree_quality_ab.txt)
+#endif
+#ifndef DRT_LEAF_MAX
+#define DRT_LEAF_MAX 3       // triangles per leaf slot (unary-coded in 3 bits of WideNode::meta: at most 3)
+#endif
 #define DRT_MEDIAN_LEVEL 40  // deeper than this: forced median splits (bounds the tree depth)
 #define DRT_BIN_WORDS 7      // count, lo xyz, hi xyz
 
