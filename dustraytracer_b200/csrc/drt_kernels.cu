@@ -741,6 +741,13 @@ __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(cons
 	__syncthreads();
 	for (int i = tid; i < n; i += nt) prim_bounds(A, i);
 	__syncthreads();
+#ifdef DRT_BUILD_SMALL_TIMING
+	long long tc = clock64();
+#define DRT_BS_TICK(SLOT) do { if (tid == 0 && (SLOT) < DRT_BUILD_SMALL_RESULT_INTS) { const long long now = clock64(); result[SLOT] = (int)(now - tc); tc = now; } } while (0)
+#else
+#define DRT_BS_TICK(SLOT) do { } while (0)
+#endif
+	DRT_BS_TICK(8);
 	int level_start = 0, level_end = 1, level = 0, slot_base = 0, slot_end = n > DRT_SMALL_NODE ? 1 : 0, swapped = 0;
 	while (level_end > level_start) {
 		A.level_start = level_start; A.level_end = level_end; A.level = level; A.bin_slot_base = slot_base;
@@ -751,10 +758,16 @@ __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(cons
 			for (int i = tid; i < n; i += nt) bin_prim(A, i);
 			__syncthreads();
 		}
+		DRT_BS_TICK(9 + 3 * level);
+		// (one thread per node, nodes packed into as few warps as possible: the split is a long serial routine working in local
+		// memory; dealing the nodes to 32 warps instead -- one or a few active lanes per warp -- measured 1.6x SLOWER, because a
+		// warp's local-memory lines are then fetched for single lanes and 1024 threads' local arrays fall out of L1)
 		for (int j = tid; j < level_end - level_start; j += nt) split_node(A, j);
 		__syncthreads();
+		DRT_BS_TICK(10 + 3 * level);
 		for (int i = tid; i < n; i += nt) partition_prim(A, i);
 		__syncthreads();
+		DRT_BS_TICK(11 + 3 * level);
 		if (tid == 0) { s_count[0] = A.state->node_count; s_count[1] = A.state->bin_slots; }
 		__syncthreads();
 		int* t = A.idx_in; A.idx_in = A.idx_out; A.idx_out = t;
@@ -770,6 +783,7 @@ __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(cons
 	while (we > ws) {
 		for (int j = tid; j < we - ws; j += nt) collapse_node(A, A.idx_in, ws, we, j);
 		__syncthreads();
+		DRT_BS_TICK(57 + wl);
 		if (tid == 0) s_count[0] = A.state->wide_count;
 		__syncthreads();
 		ws = we; we = s_count[0]; wl++;
@@ -783,7 +797,8 @@ __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(cons
 cudaError_t launch_build_small(const BuildArrays& A, int* result, cudaStream_t s)
 {
 	if (A.n <= 0) return cudaErrorInvalidValue;
-	// one thread per primitive up to the block limit (fewer threads = cheaper barriers; the passes are strided loops)
+	// one thread per primitive up to the block limit (the passes are strided loops; fewer threads = cheaper barriers and less
+	// local memory competing for L1)
 	int threads = ((A.n + 31) / 32) * 32;
 	if (threads < 64) threads = 64;
 	if (threads > DRT_BUILD_SMALL_THREADS) threads = DRT_BUILD_SMALL_THREADS;

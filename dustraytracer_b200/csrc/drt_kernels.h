@@ -57,6 +57,7 @@ cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* i
 // Single-launch build for small scenes (k_build_small: one block runs the whole level loop). `result` = 6 device ints:
 // bvh2 nodes, wide nodes, levels, wide levels, triangles emitted, 1 if the final index array is A.idx_out.
 #define DRT_BUILD_SMALL_THREADS 1024
+#define DRT_BUILD_SMALL_RESULT_INTS 64 /* 6 used; the rest carries per-pass clocks in DRT_BUILD_SMALL_TIMING measurement builds */
 #ifndef DRT_BUILD_SMALL_MAX_TRIS
 #define DRT_BUILD_SMALL_MAX_TRIS 2048
 #endif
