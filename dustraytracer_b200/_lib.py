@@ -61,7 +61,7 @@ class drt_counters(ctypes.Structure):
 assert ctypes.sizeof(drt_camera) == 88 and ctypes.sizeof(drt_settings) == 64 and ctypes.sizeof(drt_material) == 44
 
 DRT_RGBA32F, DRT_RGBA8, DRT_ACCUM_RGB32F = 0, 1, 2
-DRT_FLAG_STRICT, DRT_FLAG_HOST_ARG_ORDER, DRT_FLAG_STATS, DRT_FLAG_EXTENDED_MATERIALS, DRT_FLAG_WATERTIGHT = 1, 2, 4, 8, 16
+DRT_FLAG_STRICT, DRT_FLAG_HOST_ARG_ORDER, DRT_FLAG_STATS, DRT_FLAG_EXTENDED_MATERIALS, DRT_FLAG_WATERTIGHT, DRT_FLAG_NO_TILE_ORDER = 1, 2, 4, 8, 16, 32
 
 _vp, _i, _u, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint32, ctypes.c_size_t
 _P = ctypes.POINTER
@@ -99,6 +99,7 @@ SIGNATURES = {
     "drt_renderer_height": (_u, [_vp]),
     "drt_renderer_kernel_launches": (_i, [_vp]),
     "drt_renderer_last_variant": (_i, [_vp]),
+    "drt_renderer_last_launch_ordered": (_i, [_vp]),
     "drt_renderer_readback": (_i, [_vp, _i, _vp, _sz]),
     "drt_renderer_upload_accum": (_i, [_vp, _vp, _sz, _u]),
     "drt_renderer_accum_device_ptr": (_i, [_vp, _P(_vp), _P(_sz)]),

@@ -295,6 +295,10 @@ class Renderer:
         """Kernel variant the last Render ran (automatic selection resolved)."""
         return _lib.lib().drt_renderer_last_variant(self._h)
 
+    def last_launch_ordered(self):
+        """True if the last render launch ran its blocks in cost order (second and later batched launches of a view)."""
+        return bool(_lib.lib().drt_renderer_last_launch_ordered(self._h))
+
     def trace_primary(self, cam, scene, frame_index=1):
         """Parity probe: structured array (prim_id, t, u, v) per pixel, p = x + y*W."""
         w, h = self.getBufferWidth(), self.getBufferHeight()

@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <chrono>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -113,6 +114,7 @@ struct drt_scene {
 	DevBuf<uint32_t> texels;
 	SceneView view;
 	drt_scene_stats stats;
+	uint64_t build_serial = 0; // changes with every drt_scene_build_bvh (a renderer's cost order is tied to the tree it was measured on)
 	drt_scene() { memset(&view, 0, sizeof(view)); memset(&stats, 0, sizeof(stats)); }
 };
 
@@ -132,6 +134,20 @@ struct drt_renderer {
 	DevBuf<Counters> counters;
 	DevBuf<unsigned> work_queue; // pixel-queue kernel: next tile, warps that have left (the kernel leaves both at zero)
 	DevBuf<uint8_t> pool_scratch; // sample-pool kernel (variants 22 / 23): pool colours of a launch, grown on demand
+	// cost-ordered launches: the first batched launch of a view records the resident time of every block's tiles (block_cost); the next
+	// launches of the SAME view (scene build, camera, settings, size, tile schedule) run the blocks by descending cost (block_order),
+	// so that the launch drains on its cheapest blocks instead of on whatever sits at the end of the image
+	struct OrderKey {
+		const drt_scene* scene; uint64_t build_serial; drt_camera cam; drt_settings settings;
+		uint32_t width, height, tile_first, tile_stride, blocks, block_threads, flags, pad;
+	};
+	DevBuf<uint32_t> block_cost[2], block_order; // two cost arrays: one complete (it feeds the sort), one being recorded
+	OrderKey order_key;
+	bool order_key_valid = false;
+	int cost_ready = -1;       // index of the complete cost array (-1: none)
+	int cost_quality = 0;      // what it was measured on: 1 = the one-sample probe launch, 2 = a whole batched launch
+	int order_quality = 0;     // quality of the costs block_order was sorted from (0: no order)
+	bool last_ordered = false; // the last launch ran in cost order
 	DevBuf<uint8_t> rg_overflow; // regrouping kernel (variant 16): traversal-stack overflow area, allocated at its first launch
 	DevBuf<Hit> hits;
 	DevBuf<uint8_t> staging;
@@ -513,6 +529,8 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* param
 	scene->stats.device_bytes = scene->nodes.bytes() + scene->nodes_f32.bytes() + scene->tris.bytes() + scene->tris_v.bytes() + scene->shade.bytes() + scene->materials.bytes()
 		+ scene->texdesc.bytes() + scene->texels.bytes();
 	scene->built = true;
+	static std::atomic<uint64_t> serial{ 0 };
+	scene->build_serial = ++serial;
 	return DRT_OK;
 }
 
@@ -756,6 +774,8 @@ static int make_render_params(drt_renderer* r, const drt_camera* cam, const drt_
 	return DRT_OK;
 }
 
+extern "C" int drt_renderer_last_launch_ordered(const drt_renderer* r) { return r && r->last_ordered ? 1 : 0; }
+
 #define DRT_AUTOTUNE_CANDIDATES 3
 #define DRT_AUTOTUNE_PERIOD 256
 #define DRT_AUTOTUNE_PERIOD_MAX 4096
@@ -874,9 +894,71 @@ static int render_launch(drt_renderer* r, const drt_camera* cam, const drt_scene
 	bool probing = false;
 	const int candidate = autotune_pick(r, scene, P, probing);
 	if (candidate >= 0) autotune_apply(candidate, n, cfg);
+	// cost order (see drt_renderer::OrderKey): launches of DRT_ORDER_MIN_SPP samples or more over at least two waves of blocks
+	int record_into = -1; // cost array this launch records into
+	uint32_t probe = 0;   // samples of the probe launch
+	{
+		const uint32_t threads = cfg.block_threads > 0 ? (uint32_t)cfg.block_threads : 128u, wpb = threads / 32u;
+		const long long all_tiles = (long long)((r->width + 7) / 8) * ((r->height + 3) / 4);
+		const long long tiles = all_tiles > r->tile_first ? (all_tiles - r->tile_first + r->tile_stride - 1) / r->tile_stride : 0;
+		const long long blocks = wpb ? (tiles + wpb - 1) / wpb : 0;
+		const bool order_ok = !(r->flags & (DRT_FLAG_NO_TILE_ORDER | DRT_FLAG_EXTENDED_MATERIALS)) && candidate < 0 && n >= DRT_ORDER_MIN_SPP &&
+			P.shade.render_mode == 0 && blocks >= 2ll * r->sm_count * 6 && blocks < 0x7fffffffll;
+		if (!order_ok) { r->order_key_valid = false; r->cost_ready = -1; r->cost_quality = r->order_quality = 0; }
+		else {
+			drt_renderer::OrderKey k;
+			memset(&k, 0, sizeof(k));
+			k.scene = scene; k.build_serial = scene->build_serial; k.cam = *cam; if (settings) k.settings = *settings;
+			k.width = r->width; k.height = r->height; k.tile_first = r->tile_first; k.tile_stride = r->tile_stride;
+			k.blocks = (uint32_t)blocks; k.block_threads = threads; k.flags = r->flags;
+			k.settings.max_samples = 0; // (how many samples may still come does not change what a tile costs)
+			if (!r->order_key_valid || memcmp(&k, &r->order_key, sizeof(k)) != 0) { // a new view
+				r->order_key = k; r->order_key_valid = true;
+				r->cost_ready = -1; r->cost_quality = r->order_quality = 0;
+				if (r->block_order.n < (size_t)blocks) {
+					DRT_CUDA(cudaStreamSynchronize(r->stream));
+					DRT_CUDA(r->block_cost[0].alloc((size_t)blocks)); DRT_CUDA(r->block_cost[1].alloc((size_t)blocks)); DRT_CUDA(r->block_order.alloc((size_t)blocks));
+				}
+				// a long launch does not wait for the NEXT launch of the view to be ordered: its first sample is launched on its own
+				// and records the costs (128 paths per block)
+				static const uint32_t probe_spp = getenv("DRT_ORDER_PROBE_SPP") ? (uint32_t)atoi(getenv("DRT_ORDER_PROBE_SPP")) : 1u; // (0: never; measurement knob)
+				if (probe_spp > 0 && n >= DRT_ORDER_PROBE_MIN_SPP && probe_spp < n) probe = probe_spp;
+			}
+			if (r->order_quality < 2) record_into = r->cost_ready == 0 ? 1 : 0; // until the order rests on a whole launch's costs
+		}
+	}
 	DRT_CUDA(cudaEventRecord(r->ev0, r->stream));
+	if (probe) {
+		// (the pixel sums see the same additions in the same order as in one launch)
+		RenderParams A = P;
+		A.n_samples = probe;
+		A.total_samples = (float)(r->samples_done + probe);
+		A.block_cost = r->block_cost[record_into].p;
+		int probe_variant = -1;
+		DRT_CUDA(cudaMemsetAsync(A.block_cost, 0, (size_t)r->order_key.blocks * sizeof(uint32_t), r->stream));
+		DRT_CUDA(launch_render(A, cfg, r->stream, &r->kernel_launches, &probe_variant));
+		if (variant_honours_block_order(probe_variant)) { r->cost_ready = record_into; r->cost_quality = 1; record_into = 1 - record_into; }
+		P.frame_first += probe * r->stride;
+		P.n_samples = n - probe;
+	}
+	if (r->cost_ready >= 0) {
+		if (r->cost_quality > r->order_quality) {
+			DRT_CUDA(launch_block_order(r->block_cost[r->cost_ready].p, r->block_order.p, (int)r->order_key.blocks, r->stream));
+			r->kernel_launches++;
+			r->order_quality = r->cost_quality;
+		}
+		P.block_order = r->block_order.p;
+	}
+	if (record_into >= 0) {
+		P.block_cost = r->block_cost[record_into].p;
+		DRT_CUDA(cudaMemsetAsync(P.block_cost, 0, (size_t)r->order_key.blocks * sizeof(uint32_t), r->stream));
+	}
 	DRT_CUDA(launch_render(P, cfg, r->stream, &r->kernel_launches, &r->last_variant));
 	DRT_CUDA(cudaEventRecord(r->ev1, r->stream));
+	const bool honoured = variant_honours_block_order(r->last_variant);
+	r->last_ordered = P.block_order != nullptr && honoured;
+	if (record_into >= 0 && honoured) { r->cost_ready = record_into; r->cost_quality = 2; }
+	if (r->order_key_valid && !honoured) { r->order_key_valid = false; r->cost_ready = -1; r->cost_quality = r->order_quality = 0; }
 	*candidate_out = candidate; *probing_out = probing;
 	r->samples_done += n;
 	r->frame_index += n;

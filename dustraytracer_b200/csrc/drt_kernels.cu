@@ -33,13 +33,16 @@ namespace drt {
 
 namespace {
 
+// group of tiles this block renders: its own index, or the entry of the cost order (RenderParams::block_order)
+__device__ __forceinline__ uint32_t group_of_block(const RenderParams& P) { return P.block_order ? P.block_order[blockIdx.x] : blockIdx.x; }
+
 __device__ __forceinline__ void pixel_of_thread(int width, int height, int warps_per_block, uint32_t tile_first, uint32_t tile_stride,
-	int& x, int& y, bool& valid)
+	int& x, int& y, bool& valid, uint32_t group = blockIdx.x)
 {
 	// 8x4 pixel tile per warp; tiles numbered row-major over the image; a launch owns tiles first, first+stride, ...
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int tiles_x = (width + 7) >> 3;
-	const long long tile = ((long long)blockIdx.x * warps_per_block + warp) * tile_stride + tile_first;
+	const long long tile = ((long long)group * warps_per_block + warp) * tile_stride + tile_first;
 	const int ty = (int)(tile / tiles_x), tx = (int)(tile - (long long)ty * tiles_x);
 	x = tx * 8 + (lane & 7);
 	y = ty * 4 + (lane >> 3);
@@ -76,7 +79,8 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 {
 	int x, y;
 	bool valid;
-	pixel_of_thread(P.width, P.height, warps_per_block, P.tile_first, P.tile_stride, x, y, valid);
+	pixel_of_thread(P.width, P.height, warps_per_block, P.tile_first, P.tile_stride, x, y, valid, VARIANT >= 2 ? group_of_block(P) : blockIdx.x);
+	const unsigned t_begin = (VARIANT >= 2 && P.block_cost) ? (unsigned)clock() : 0u; // (32 bits: a block lives far less than 2 s)
 	PathCounters pc;
 	pc.closest = 0; pc.shadow = 0;
 	TraceStats ts;
@@ -135,6 +139,46 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 		P.display[p] = make_float4(acc.x / P.total_samples, acc.y / P.total_samples, acc.z / P.total_samples, 1.f);
 	}
 	flush_counters(P.counters, pc, st);
+	// cost of this group of tiles for the order of the NEXT launch of the same view: the clocks its slowest warp was resident
+	if (VARIANT >= 2 && P.block_cost && (threadIdx.x & 31) == 0) atomicMax(&P.block_cost[group_of_block(P)], (((unsigned)clock() - t_begin) >> 4) + 1u);
+}
+
+// One block: block_order = the indices 0 .. n-1 sorted by DESCENDING cost (counting sort over DRT_ORDER_BUCKETS linear buckets of
+// cost / max cost; the order inside a bucket is whatever the atomics give -- any order renders the same image).
+#define DRT_ORDER_BUCKETS 2048
+__global__ void __launch_bounds__(1024) k_block_order(const uint32_t* __restrict__ cost, uint32_t* __restrict__ order, int n)
+{
+	__shared__ unsigned hist[DRT_ORDER_BUCKETS];
+	__shared__ unsigned scan[DRT_ORDER_BUCKETS];
+	__shared__ unsigned smax;
+	const int tid = (int)threadIdx.x, nt = (int)blockDim.x;
+	if (tid == 0) smax = 1u;
+	for (int b = tid; b < DRT_ORDER_BUCKETS; b += nt) hist[b] = 0u;
+	__syncthreads();
+	unsigned m = 1u;
+	for (int i = tid; i < n; i += nt) m = max(m, cost[i]);
+	m = __reduce_max_sync(0xffffffffu, m);
+	if ((tid & 31) == 0) atomicMax(&smax, m);
+	__syncthreads();
+	const unsigned long long mx = smax;
+	for (int i = tid; i < n; i += nt) atomicAdd(&hist[(DRT_ORDER_BUCKETS - 1) - (unsigned)(((unsigned long long)cost[i] * (DRT_ORDER_BUCKETS - 1)) / mx)], 1u);
+	__syncthreads();
+	// exclusive prefix sum of the bucket counts (Hillis-Steele on 2048 words, two per thread)
+	for (int b = tid; b < DRT_ORDER_BUCKETS; b += nt) scan[b] = hist[b];
+	__syncthreads();
+	for (int d = 1; d < DRT_ORDER_BUCKETS; d <<= 1) {
+		unsigned v[DRT_ORDER_BUCKETS / 1024];
+		for (int k = 0, b = tid; b < DRT_ORDER_BUCKETS; b += nt, k++) v[k] = b >= d ? scan[b - d] : 0u;
+		__syncthreads();
+		for (int k = 0, b = tid; b < DRT_ORDER_BUCKETS; b += nt, k++) scan[b] += v[k];
+		__syncthreads();
+	}
+	for (int b = tid; b < DRT_ORDER_BUCKETS; b += nt) hist[b] = scan[b] - hist[b]; // first position of the bucket
+	__syncthreads();
+	for (int i = tid; i < n; i += nt) {
+		const unsigned b = (DRT_ORDER_BUCKETS - 1) - (unsigned)(((unsigned long long)cost[i] * (DRT_ORDER_BUCKETS - 1)) / mx);
+		order[atomicAdd(&hist[b], 1u)] = (uint32_t)i;
+	}
 }
 
 // Phased kernel with the SHADE-only lane state in shared memory (drt_phased.cuh render_warp_cold).
@@ -680,6 +724,13 @@ cudaError_t launch_trace_rays(const SceneView& sc, const float* org_dev, const f
 	if (cfg.strict) { if (f32) { if (tri2) DRT_TR(true, NODE_FMT_F32, true); else DRT_TR(true, NODE_FMT_F32, false); } else { if (tri2) DRT_TR(true, NODE_FMT_Q8, true); else DRT_TR(true, NODE_FMT_Q8, false); } }
 	else { if (f32) { if (tri2) DRT_TR(false, NODE_FMT_F32, true); else DRT_TR(false, NODE_FMT_F32, false); } else { if (tri2) DRT_TR(false, NODE_FMT_Q8, true); else DRT_TR(false, NODE_FMT_Q8, false); } }
 #undef DRT_TR
+	return cudaGetLastError();
+}
+
+cudaError_t launch_block_order(const uint32_t* cost, uint32_t* order, int n, cudaStream_t s)
+{
+	if (n <= 0) return cudaSuccess;
+	k_block_order<<<1, 1024, 0, s>>>(cost, order, n);
 	return cudaGetLastError();
 }
 

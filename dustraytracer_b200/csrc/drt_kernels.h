@@ -53,6 +53,12 @@ int sample_pool_size(uint32_t n_samples, int override_r);
 size_t sample_pool_scratch_bytes(long long tiles, int pool_r);
 // Bytes of the regrouping kernel's traversal-stack overflow area for a device of `sms` multiprocessors (RenderParams::rg_overflow).
 size_t regroup_overflow_bytes(int sms);
+// Cost-ordered launches (RenderParams::block_order / block_cost): order[0 .. n-1] = group indices by descending cost.
+cudaError_t launch_block_order(const uint32_t* cost, uint32_t* order, int n, cudaStream_t s);
+// (honoured by the fixed-tile phased kernels: launch_render's variant_out in {2 .. 8, 15, 17, 18, 21, 22, 23})
+inline bool variant_honours_block_order(int v) { return (v >= 2 && v <= 8) || v == 15 || v == 17 || v == 18 || v == 21 || v == 22 || v == 23; }
+#define DRT_ORDER_MIN_SPP 16
+#define DRT_ORDER_PROBE_MIN_SPP 64 /* launches this long pay a one-sample probe launch to be ordered themselves */
 cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s);
 // Single-launch build for small scenes (k_build_small: one block runs the whole level loop). `result` = 6 device ints:
 // bvh2 nodes, wide nodes, levels, wide levels, triangles emitted, 1 if the final index array is A.idx_out.

@@ -106,6 +106,10 @@ struct RenderParams {
 	unsigned* work_queue;   // 2 words, zero between launches: next tile, warps that have left (pixel-queue kernel)
 	uint32_t tile_first, tile_stride; // image-tile sharding: this launch owns the 8x4 tiles first, first+stride, ... (row-major tile index)
 	void* pool_scratch;     // sample-pool kernel (variants 22 / 23): pool colours, float4 x 32 x R per owned tile (may be null)
+	// cost-ordered launch (fixed-tile kernels): block b renders the owned tiles 4 * block_order[b] + warp instead of 4 * b + warp, most expensive
+	// groups first, so that the launch drains on its cheapest blocks; block_cost[g] receives the rays of group g (either may be null)
+	const uint32_t* block_order;
+	uint32_t* block_cost;
 	void* rg_overflow;      // regrouping kernel (variant 16): traversal-stack entries beyond the shared-memory ones, DRT_PSTACK x 8 bytes per resident context (may be null)
 };
 

@@ -115,6 +115,9 @@ typedef enum drt_flags {
 	DRT_FLAG_STRICT = 1,       /* separately-rounded fp32 in the reference's operation order (parity mode)      */
 	DRT_FLAG_HOST_ARG_ORDER = 2, /* draw randomUnitVec3 components right-to-left like the g++-compiled oracle     */
 	DRT_FLAG_STATS = 4,        /* count node visits / triangle tests (slower; for the roofline's V and T terms) */
+	DRT_FLAG_NO_TILE_ORDER = 32, /* off: batched launches (>= 16 samples, >= two waves of blocks) of a view that was rendered before run their
+	                                blocks by descending measured cost, so that the launch drains on its cheapest tiles; results do not depend
+	                                on the order (bit-identical); no counterpart in the reference. Set to keep the row-major order */
 	DRT_FLAG_WATERTIGHT = 16,  /* production arithmetic only (ignored with DRT_FLAG_STRICT): the watertight ray / triangle test of Woop,
 	                              Benthin, Wald (JCGT 2013) replaces the reference's Moller-Trumbore (Intersection.cu:4-36), whose
 	                              absolute determinant epsilon (1e-6, physical_units.hpp:12) drops small / distant triangles and
@@ -180,6 +183,7 @@ int drt_renderer_set_tuning(drt_renderer* r, int32_t variant, int32_t block_thre
 void drt_renderer_destroy(drt_renderer* r);
 int drt_renderer_kernel_launches(const drt_renderer* r); /* kernels launched by this renderer so far */
 int drt_renderer_last_variant(const drt_renderer* r);    /* kernel variant the last render launch ran (automatic selection resolved) */
+int drt_renderer_last_launch_ordered(const drt_renderer* r); /* 1 if the last render launch ran its blocks in cost order (DRT_FLAG_NO_TILE_ORDER) */
 /* Checkpoint / resume: restore accumulation sums (3 floats / pixel) and the number of samples they hold. */
 int drt_renderer_upload_accum(drt_renderer* r, const float* rgb32f, size_t bytes, uint32_t samples_done);
 /* Sample-range sharding across GPUs: this renderer renders frame indices first, first+stride, ... (default 1, 1). */

@@ -523,3 +523,66 @@ def test_scenes_above_the_single_launch_limit_use_the_level_synchronous_builder(
     s = drt.Scene.from_triangles(O.soup_triangles(2049).reshape(2049, 3, 3))
     s.build_bvh()
     assert s.stats()["build_launches"] > 1
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# cost-ordered launches
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,variant", [("room", -1), ("animemaid", -1), ("dense_monkey", 4), ("room", 15)])
+def test_cost_ordered_launches_render_the_same_bits(drt, name, variant):
+    """The first batched launch of a view records what every block of tiles cost; the following launches of the same view run the
+    blocks by descending cost. The order must not show in the results: accumulation, display and ray counters of every launch
+    equal those of a renderer with DRT_FLAG_NO_TILE_ORDER (row-major order), in parity and production arithmetic, across a
+    reset, and the order must be dropped when the camera, the settings or the image size change."""
+    scene = gpu_scene(drt, name)
+    W, H = 1280, 720   # 160 x 180 tiles = 7200 blocks: more than two waves (2 x 148 x 6 = 1776 blocks)
+    st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=3, max_samples=100000)
+
+    def run(flags):
+        r = drt.Renderer(flags=flags)
+        r.set_tuning(variant, 0)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(W, H)
+        cam = drt.Camera()
+        out, ordered = [], []
+
+        def launch(n, c):
+            r.Render(c, scene, n)
+            ordered.append(r.last_launch_ordered())
+            out.append((bits(r.readback(drt.DRT_ACCUM_RGB32F)).copy(), bits(r.readback(drt.DRT_RGBA32F)).copy(), r.counters()))
+
+        cam2 = drt.Camera()
+        cam2.position[0] = 0.3
+        launch(16, cam)       # records costs
+        launch(16, cam)       # ordered
+        r.resetAccumulationBuffer()
+        launch(20, cam)       # same view after a reset, another sample count: still ordered
+        launch(16, cam2)      # the camera moved: a new view, records again
+        launch(16, cam2)      # ordered
+        launch(8, cam2)       # fewer than DRT_ORDER_MIN_SPP samples: row-major, and the state is dropped
+        launch(16, cam2)      # records again
+        r.m_RendererSettings = drt.RendererSettings(enable_sunlight=0, ray_bounce_limit=3, max_samples=100000)
+        launch(16, cam2)      # other settings: a new view
+        return out, ordered
+
+    for flags in (STRICT, 0):
+        a, oa = run(flags)
+        b, ob = run(flags | drt.DRT_FLAG_NO_TILE_ORDER)
+        assert oa == [False, True, True, False, True, False, False, False], oa
+        assert ob == [False] * 8
+        for i, ((acc_a, dis_a, c_a), (acc_b, dis_b, c_b)) in enumerate(zip(a, b)):
+            assert np.array_equal(acc_a, acc_b) and np.array_equal(dis_a, dis_b), (flags, i)
+            assert c_a == c_b, (flags, i)
+
+    # a LONG first launch of a view (>= 64 samples) is split into a one-sample launch that records the costs and the rest in cost
+    # order: ordered at once, and the same bits as the single row-major launch
+    res = []
+    for flags in (0, drt.DRT_FLAG_NO_TILE_ORDER):
+        r = drt.Renderer(flags=flags)
+        r.set_tuning(variant, 0)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(W, H)
+        r.Render(drt.Camera(), scene, 70)
+        res.append((r.last_launch_ordered(), bits(r.readback(drt.DRT_ACCUM_RGB32F)).copy(), bits(r.readback(drt.DRT_RGBA32F)).copy(), r.counters(), r.getSampleCount()))
+    assert res[0][0] and not res[1][0]
+    assert np.array_equal(res[0][1], res[1][1]) and np.array_equal(res[0][2], res[1][2]) and res[0][3] == res[1][3] and res[0][4] == res[1][4]
