@@ -135,6 +135,11 @@ def main():
         c = r.counters()
         rays = c["closest_rays"] + c["shadow_rays"]
         img = r.readback(drt.DRT_RGBA32F)
+        ordered_first = r.last_launch_ordered()
+        r.resetAccumulationBuffer()
+        ms_repeat = r.Render(cam, scene, spp)   # the same view again: blocks in the cost order measured by the launch before
+        out.update({"ms_repeat": round(ms_repeat, 3), "Mrays_s_repeat": round(rays / ms_repeat / 1e3, 1), "ordered": [ordered_first, r.last_launch_ordered()],
+                    "variant": r.last_variant()})
         out.update({"ms": round(ms, 3), "Mrays_s": round(rays / ms / 1e3, 1), "Msamples_s": round(W * H * spp / ms / 1e3, 1),
                     "rays": rays, "mean_ldr": round(float(img[:, :, :3].mean()), 5), "finite": bool(np.isfinite(img).all())})
         ref_ms = ref_cuda(name, cam_bytes, O.settings_bytes(sun=bool(sun), bounces=bounces, max_samples=1 << 30), W, H, a.ref_frames) if a.ref_frames > 0 else None
