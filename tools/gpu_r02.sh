@@ -17,7 +17,7 @@ launches)
 ncu256)
   # the benchmarked launch itself (256 spp), short metric list
   DRT_BENCH_SKIP_BASELINES=1 timeout 600 python bench.py --steps 1 --warmup 3 > gpurun_out/plain256.log 2>&1 &&
-  DRT_BENCH_SKIP_BASELINES=1 timeout 1200 ncu --metrics $METRICS --clock-control none -k regex:k_render -c 1 -o gpurun_out/render256 -f python bench.py --steps 1 --warmup 3 > gpurun_out/ncu256.log 2>&1 ;;
+  DRT_BENCH_SKIP_BASELINES=1 timeout 1200 ncu --metrics $METRICS --clock-control none -k regex:k_render --launch-skip 3 -c 1 -o gpurun_out/render256 -f python bench.py --steps 1 --warmup 3 > gpurun_out/ncu256.log 2>&1 ;;
 ncufull16)
   DRT_BENCH_SKIP_BASELINES=1 DRT_BENCH_SPP=16 timeout 600 python bench.py --steps 1 --warmup 3 > gpurun_out/plain16.log 2>&1 &&
   DRT_BENCH_SKIP_BASELINES=1 DRT_BENCH_SPP=16 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k_render -c 1 -o gpurun_out/render_full -f python bench.py --steps 1 --warmup 3 > gpurun_out/ncu_full.log 2>&1 ;;
