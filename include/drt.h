@@ -115,9 +115,6 @@ typedef enum drt_flags {
 	DRT_FLAG_STRICT = 1,       /* separately-rounded fp32 in the reference's operation order (parity mode)      */
 	DRT_FLAG_HOST_ARG_ORDER = 2, /* draw randomUnitVec3 components right-to-left like the g++-compiled oracle     */
 	DRT_FLAG_STATS = 4,        /* count node visits / triangle tests (slower; for the roofline's V and T terms) */
-	DRT_FLAG_NO_TILE_ORDER = 32, /* off: batched launches (>= 16 samples, >= two waves of blocks) of a view that was rendered before run their
-	                                blocks by descending measured cost, so that the launch drains on its cheapest tiles; results do not depend
-	                                on the order (bit-identical); no counterpart in the reference. Set to keep the row-major order */
 	DRT_FLAG_WATERTIGHT = 16,  /* production arithmetic only (ignored with DRT_FLAG_STRICT): the watertight ray / triangle test of Woop,
 	                              Benthin, Wald (JCGT 2013) replaces the reference's Moller-Trumbore (Intersection.cu:4-36), whose
 	                              absolute determinant epsilon (1e-6, physical_units.hpp:12) drops small / distant triangles and
@@ -127,7 +124,13 @@ typedef enum drt_flags {
 	                              reference loads but ignores (Material.cuh:10-22; RayGen.cuh never reads them):
 	                              emissive_factor, metallic + roughness (mirror / fuzzy reflection), transmission +
 	                              refractive_index (dielectric, with the reference's own dead helpers refract /
-	                              reflectance, Random.cu:26-40). Off: exactly the reference's shading. */
+	                              reflectance, Random.cu:26-40). Off: exactly the reference's shading. */,
+	DRT_FLAG_NO_TILE_ORDER = 32 /* keep the row-major block order. Without this flag a renderer measures, per block of 4 tiles, how long
+	                              the block was resident, and runs the blocks of the following batched launches of the same view
+	                              (>= 16 samples, >= two waves of blocks; a launch of >= 64 samples is ordered itself, after a
+	                              one-sample probe launch) most expensive first, so that a launch drains on its cheapest tiles.
+	                              The results do not depend on the order (bit-identical images and counters); no counterpart in the
+	                              reference, whose launch is row-major (Renderer.hpp:43-44). */
 } drt_flags;
 
 /* ---- scene: replaces Scene::loadGLTFmodel (Scene.cu:181-317) and BVHBuilder::build* (BVHBuilder.cu:11-145) ---- */
