@@ -912,6 +912,7 @@ static int render_launch(drt_renderer* r, const drt_camera* cam, const drt_scene
 			k.width = r->width; k.height = r->height; k.tile_first = r->tile_first; k.tile_stride = r->tile_stride;
 			k.blocks = (uint32_t)blocks; k.block_threads = threads; k.flags = r->flags;
 			k.settings.max_samples = 0; // (how many samples may still come does not change what a tile costs)
+			k.settings._pad0 = 0; k.settings._pad1 = 0; // (padding of the reference's struct: whatever the caller's memory held)
 			if (!r->order_key_valid || memcmp(&k, &r->order_key, sizeof(k)) != 0) { // a new view
 				r->order_key = k; r->order_key_valid = true;
 				r->cost_ready = -1; r->cost_quality = r->order_quality = 0;
