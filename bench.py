@@ -386,11 +386,11 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     W, H, SPP = WORKLOAD["width"], WORKLOAD["height"], WORKLOAD["spp"]
-    strong = args.scaling == "strong" or args.shard in ("tiles", "p2p")
-    if strong and args.shard == "samples" and SPP % world:
+    strong = args.scaling == "strong" or args.shard in ("tiles", "p2p", "fused")
+    if strong and args.shard in ("samples", "fused") and SPP % world:
         raise SystemExit("bench.py: strong sample-range sharding needs spp (%d) divisible by the number of GPUs (%d)" % (SPP, world))
     # samples per pixel THIS rank renders per step: strong scaling = one SPP-sample frame split over the ranks
-    rank_spp = SPP // world if (strong and args.shard == "samples") else SPP
+    rank_spp = SPP // world if (strong and args.shard in ("samples", "fused")) else SPP
     frame_spp = SPP if strong else SPP * world  # samples per pixel of the frame one step produces (all GPUs together)
 
     scene = drt.Scene()
@@ -404,8 +404,11 @@ def run_ours(args, rank, world, local_rank):
     r.ResizeBuffer(W, H)
     stream = torch.cuda.current_stream(dev)
     r.set_stream(stream.cuda_stream)
-    p2p = args.shard == "p2p"
+    fused = args.shard == "fused" and world > 1   # sample ranges, every rank's kernel ADDS its sums into rank 0's buffer (no collective)
+    p2p = args.shard == "p2p" or fused           # frame buffers of rank 0 shared over CUDA IPC / NVLink
     tiles = args.shard in ("tiles", "p2p")
+    if fused:
+        r.set_accumulate_add(True)
     if tiles:
         # image-tile sharding (strong scaling of one frame): rank g owns the 8x4 tiles g, g+world, ... of every frame
         r.set_tile_schedule(rank, world)
@@ -438,6 +441,8 @@ def run_ours(args, rank, world, local_rank):
         r.Render(cam, scene, rank_spp)       # (returns with this rank's share done: its tiles stored / its frame indices summed)
         if p2p and world > 1:
             node_barrier.wait()              # the frame (sums and display) is complete in rank 0's buffers
+            if fused and rank == 0:
+                r.resolve(frame_spp)         # (fused: the kernels added the sums; the display buffer is derived here)
         elif world > 1:
             dist.reduce(acc_t, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
@@ -613,7 +618,8 @@ def run_ours(args, rank, world, local_rank):
             "data": "synthetic camera path over the bundled room scene (fixture re-muxed from the reference model)",
             "samples_per_s": W * H * frame_spp * args.steps / (max_ms * 1e-3),
             "config": {"workload": "room.glb 1920x1080, %d spp per %s per step, 8 bounces, sun shadow rays (BASELINE config 3)" % (SPP, "frame (all GPUs together)" if strong else "GPU"),
-                       **WORKLOAD, "parallelism": ("image-tile sharding x%d (8x4 tiles, interleaved), peer stores into rank 0's frame buffers over NVLink, no collective (host barrier in shared memory)" if p2p
+                       **WORKLOAD, "parallelism": ("sample-range sharding x%d, fused render + reduce: every rank's kernel adds its pixel sums into rank 0's accumulation buffer with fp32 atomics over NVLink, no collective (host barrier in shared memory)" if fused
+                                                   else "image-tile sharding x%d (8x4 tiles, interleaved), peer stores into rank 0's frame buffers over NVLink, no collective (host barrier in shared memory)" if p2p
                                                    else "image-tile sharding x%d (8x4 tiles, interleaved) + NCCL reduce of the accumulation buffer" if tiles
                                                    else "sample-range sharding x%d + NCCL reduce of the accumulation buffer") % world,
                        "spp_per_gpu_per_step": rank_spp, "spp_per_frame": frame_spp,
@@ -689,9 +695,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--shard", default=os.environ.get("DRT_SHARD", "samples"), choices=["samples", "tiles", "p2p"],
-                    help="N>1: sample-range sharding (weak scaling, default), image-tile sharding of each frame + reduce (strong scaling), "
-                         "or image tiles stored directly into rank 0's buffers over NVLink (p2p)")
+    ap.add_argument("--shard", default=os.environ.get("DRT_SHARD", "samples"), choices=["samples", "tiles", "p2p", "fused"],
+                    help="N>1: sample-range sharding + NCCL reduce (default), image-tile sharding of each frame + reduce, image tiles stored "
+                         "directly into rank 0's buffers over NVLink (p2p), or sample ranges added into rank 0's buffer by the render kernels (fused)")
     ap.add_argument("--scaling", default=os.environ.get("DRT_SCALING", "strong"), choices=["strong", "weak"],
                     help="N>1 with sample-range sharding: strong (default) = ONE 256-spp frame, 256/N samples per pixel per GPU + reduce + resolve; "
                          "weak = 256 spp per GPU (a 256*N-spp frame per step)")

@@ -100,6 +100,7 @@ SIGNATURES = {
     "drt_renderer_kernel_launches": (_i, [_vp]),
     "drt_renderer_last_variant": (_i, [_vp]),
     "drt_renderer_last_launch_ordered": (_i, [_vp]),
+    "drt_renderer_set_accumulate_add": (_i, [_vp, _i]),
     "drt_renderer_readback": (_i, [_vp, _i, _vp, _sz]),
     "drt_renderer_upload_accum": (_i, [_vp, _vp, _sz, _u]),
     "drt_renderer_accum_device_ptr": (_i, [_vp, _P(_vp), _P(_sz)]),

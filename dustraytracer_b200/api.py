@@ -295,6 +295,11 @@ class Renderer:
         """Kernel variant the last Render ran (automatic selection resolved)."""
         return _lib.lib().drt_renderer_last_variant(self._h)
 
+    def set_accumulate_add(self, on=True):
+        """Fused render + reduce (drt_renderer_set_accumulate_add): launches add their pixel sums into the (shared) accumulation
+        buffer with fp32 atomics; the owner of the buffer resolves."""
+        check(_lib.lib().drt_renderer_set_accumulate_add(self._h, 1 if on else 0))
+
     def last_launch_ordered(self):
         """True if the last render launch ran its blocks in cost order (second and later batched launches of a view)."""
         return bool(_lib.lib().drt_renderer_last_launch_ordered(self._h))

@@ -148,6 +148,7 @@ struct drt_renderer {
 	int cost_quality = 0;      // what it was measured on: 1 = the one-sample probe launch, 2 = a whole batched launch
 	int order_quality = 0;     // quality of the costs block_order was sorted from (0: no order)
 	bool last_ordered = false; // the last launch ran in cost order
+	bool accum_add = false;    // drt_renderer_set_accumulate_add: launches ADD their pixel sums into the frame buffer with atomics
 	DevBuf<uint8_t> rg_overflow; // regrouping kernel (variant 16): traversal-stack overflow area, allocated at its first launch
 	DevBuf<Hit> hits;
 	DevBuf<uint8_t> staging;
@@ -771,10 +772,18 @@ static int make_render_params(drt_renderer* r, const drt_camera* cam, const drt_
 	P.tile_first = r->tile_first; P.tile_stride = r->tile_stride;
 	P.rg_overflow = r->rg_overflow.p;
 	P.pool_scratch = r->pool_scratch.p;
+	P.accum_add = r->accum_add ? 1u : 0u;
 	return DRT_OK;
 }
 
 extern "C" int drt_renderer_last_launch_ordered(const drt_renderer* r) { return r && r->last_ordered ? 1 : 0; }
+
+extern "C" int drt_renderer_set_accumulate_add(drt_renderer* r, int on)
+{
+	if (!r) return fail(DRT_ERR_INVALID, "drt_renderer_set_accumulate_add: null renderer");
+	r->accum_add = on != 0;
+	return DRT_OK;
+}
 
 #define DRT_AUTOTUNE_CANDIDATES 3
 #define DRT_AUTOTUNE_PERIOD 256
@@ -892,7 +901,7 @@ static int render_launch(drt_renderer* r, const drt_camera* cam, const drt_scene
 		P.rg_overflow = r->rg_overflow.p;
 	}
 	bool probing = false;
-	const int candidate = autotune_pick(r, scene, P, probing);
+	const int candidate = r->accum_add ? -1 : autotune_pick(r, scene, P, probing);
 	if (candidate >= 0) autotune_apply(candidate, n, cfg);
 	// cost order (see drt_renderer::OrderKey): launches of DRT_ORDER_MIN_SPP samples or more over at least two waves of blocks
 	int record_into = -1; // cost array this launch records into
@@ -923,7 +932,7 @@ static int render_launch(drt_renderer* r, const drt_camera* cam, const drt_scene
 				// a long launch does not wait for the NEXT launch of the view to be ordered: its first sample is launched on its own
 				// and records the costs (128 paths per block)
 				static const uint32_t probe_spp = getenv("DRT_ORDER_PROBE_SPP") ? (uint32_t)atoi(getenv("DRT_ORDER_PROBE_SPP")) : 1u; // (0: never; measurement knob)
-				if (probe_spp > 0 && n >= DRT_ORDER_PROBE_MIN_SPP && probe_spp < n) probe = probe_spp;
+				if (probe_spp > 0 && n >= DRT_ORDER_PROBE_MIN_SPP && probe_spp < n && !r->accum_add) probe = probe_spp; // (two atomic adds per pixel would not be one)
 			}
 			if (r->order_quality < 2) record_into = r->cost_ready == 0 ? 1 : 0; // until the order rests on a whole launch's costs
 		}

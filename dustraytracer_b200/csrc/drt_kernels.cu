@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 		// every lane of the warp takes part in the vote, valid pixel or not
 		const size_t p = (size_t)x + (size_t)y * (size_t)P.width;
 		V3 acc = mk3(0.f, 0.f, 0.f);
-		if (valid) { const float4 a4 = P.accum[p]; acc = mk3(a4.x, a4.y, a4.z); }
+		if (valid && !P.accum_add) { const float4 a4 = P.accum[p]; acc = mk3(a4.x, a4.y, a4.z); }
 		__shared__ alignas(16) uint8_t lut[DRT_PERMUTE_LUT_BYTES];
 		if (VARIANT == 22 || VARIANT == 23) {
 			// sample pool: the last tune.pool samples of the tile's pixels are handed out dynamically (render_warp_phased POOL)
@@ -115,7 +115,12 @@ __global__ void __launch_bounds__(VARIANT >= 4 ? 128 : 256, VARIANT == 7 ? 8 : (
 		}
 		else
 		acc = render_warp_phased<STRICT, STATS, (VARIANT == 3 || VARIANT == 7 || VARIANT == 8) ? NODE_FMT_Q8 : NODE_FMT_F32, VARIANT == 15>(P, tune, (uint32_t)x, (uint32_t)y, valid, rtl, acc, pc, st, lut);
-		if (valid) {
+		if (valid && P.accum_add) {
+			// fused render + reduce: this launch's share of the pixel sum goes straight into the (possibly remote) frame buffer
+			float* a = &P.accum[p].x;
+			atomicAdd(a, acc.x); atomicAdd(a + 1, acc.y); atomicAdd(a + 2, acc.z);
+		}
+		else if (valid) {
 			P.accum[p] = make_float4(acc.x, acc.y, acc.z, 0.f);
 			P.display[p] = make_float4(acc.x / P.total_samples, acc.y / P.total_samples, acc.z / P.total_samples, 1.f);
 		}
@@ -579,7 +584,10 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	tune.pool = 0;
 	// the phased kernels implement NORMALMODE; the debug views go through the reference-shaped loop
 	int variant = cfg.variant;
+	// fused render + reduce (RenderParams::accum_add) exists in the fixed-tile phased kernels only
+#define DRT_NO_ACCUM_ADD do { if (P.accum_add) return cudaErrorNotSupported; } while (0)
 	if (cfg.ext_materials && P.shade.render_mode == DRT_RENDER_NORMAL) {
+		DRT_NO_ACCUM_ADD;
 		k_render_ext<STRICT, STATS><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb);
 		DRT_RAN(-2);
 		return cudaGetLastError();
@@ -594,14 +602,14 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	}
 	// variant 16: block-level regrouping (no statistics build of it: counted launches run the per-warp voting kernel)
 	if (variant == 16) {
-		if (!STATS && P.work_queue != nullptr && cfg.resident_sms > 0 && P.tile_stride > 0 && P.width < 65536 && P.height < 65536) { DRT_RAN(16); return launch_regroup<STRICT>(P, cfg, s); }
+		if (!STATS && !P.accum_add && P.work_queue != nullptr && cfg.resident_sms > 0 && P.tile_stride > 0 && P.width < 65536 && P.height < 65536) { DRT_RAN(16); return launch_regroup<STRICT>(P, cfg, s); }
 		variant = 4;
 	}
 	// variants 9 / 10: persistent warps with a pixel queue, for launches of few samples (the reference's interactive pattern is
 	// one per launch); the renderer's auto-tuner (drt_api.cu) picks between them and variant 4 by measurement.
 	if (variant >= 9 && variant <= 14) {
 		const bool queue = variant <= 10;
-		const bool ok = threads == 128 && P.width < 65536 && P.height < 65536 && (!queue || (P.work_queue != nullptr && cfg.resident_sms > 0));
+		const bool ok = threads == 128 && !P.accum_add && P.width < 65536 && P.height < 65536 && (!queue || (P.work_queue != nullptr && cfg.resident_sms > 0));
 		const bool q8 = variant == 10 || variant == 14 || P.scene.nodes_f32 == nullptr;
 		if (!ok) variant = q8 ? 7 : 4;
 		else if (queue) {
@@ -668,9 +676,10 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	else if (variant == 6) k_render<STRICT, STATS, 6><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else if (variant == 3) k_render<STRICT, STATS, 3><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 	else if (variant == 2) k_render<STRICT, STATS, 2><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
-	else if (variant == 1) k_render<STRICT, STATS, 1><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
-	else k_render<STRICT, STATS, 0><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
+	else if (variant == 1) { DRT_NO_ACCUM_ADD; k_render<STRICT, STATS, 1><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune); }
+	else { DRT_NO_ACCUM_ADD; k_render<STRICT, STATS, 0><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune); }
 	return cudaGetLastError();
+#undef DRT_NO_ACCUM_ADD
 #undef DRT_RAN
 }
 

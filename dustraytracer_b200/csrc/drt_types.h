@@ -110,6 +110,9 @@ struct RenderParams {
 	// groups first, so that the launch drains on its cheapest blocks; block_cost[g] receives the rays of group g (either may be null)
 	const uint32_t* block_order;
 	uint32_t* block_cost;
+	// fused render + reduce (sample-range sharding without a collective): the pixel sums of this launch start at zero and are ADDED to `accum` with
+	// fp32 atomics (red.global.add.f32; `accum` may be another GPU's buffer, mapped over NVLink); `display` is not written (the owner resolves)
+	uint32_t accum_add;
 	void* rg_overflow;      // regrouping kernel (variant 16): traversal-stack entries beyond the shared-memory ones, DRT_PSTACK x 8 bytes per resident context (may be null)
 };
 

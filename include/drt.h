@@ -208,6 +208,16 @@ int drt_renderer_set_tile_schedule(drt_renderer* r, uint32_t first_tile, uint32_
 int drt_renderer_export_frame_buffers(drt_renderer* r, void* handle_out);
 int drt_renderer_import_frame_buffers(drt_renderer* r, const void* handle);
 int drt_renderer_attach_frame_buffers(drt_renderer* r, drt_renderer* owner);
+/* Fused render + reduce: SAMPLE-RANGE sharding without a collective (no counterpart in the reference). With on != 0 the batched
+ * launches of this renderer start every pixel sum at zero and ADD it to the accumulation buffer with fp32 atomics
+ * (red.global.add.f32) instead of load + store, and leave the display buffer alone. Renderers that share ONE pair of frame buffers
+ * (drt_renderer_attach_frame_buffers / _import_frame_buffers: the buffers of the root, mapped over NVLink) and own different frame
+ * indices (drt_renderer_set_frame_schedule) then sum their samples in the root's buffer from inside the render kernels: compute and
+ * exchange are one kernel. The caller zeroes the buffer first (the root's reset), orders the ranks (a barrier after the launches)
+ * and calls drt_renderer_resolve(total samples) on the root. The sum is that of the per-renderer partial sums, as with the
+ * reduce; with more than two renderers the ORDER of those additions, and with it the last bit, varies from run to run.
+ * Fixed-tile kernels only: debug views, extended materials and explicit variants 0 / 1 / 9-14 / 16 return DRT_ERR_CUDA. */
+int drt_renderer_set_accumulate_add(drt_renderer* r, int on);
 int drt_renderer_resize(drt_renderer* r, uint32_t width, uint32_t height);
 /* Renders up to n_samples further samples in one batch (the reference renders one per call) and updates the
  * display buffer; stops at settings->max_samples like Renderer.cu:82. ms = device time of the launch(es). */

@@ -586,3 +586,57 @@ def test_cost_ordered_launches_render_the_same_bits(drt, name, variant):
         res.append((r.last_launch_ordered(), bits(r.readback(drt.DRT_ACCUM_RGB32F)).copy(), bits(r.readback(drt.DRT_RGBA32F)).copy(), r.counters(), r.getSampleCount()))
     assert res[0][0] and not res[1][0]
     assert np.array_equal(res[0][1], res[1][1]) and np.array_equal(res[0][2], res[1][2]) and res[0][3] == res[1][3] and res[0][4] == res[1][4]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# fused render + reduce: sample ranges added into one shared buffer by the render kernels (drt_renderer_set_accumulate_add)
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,variant", [("room", -1), ("dense_monkey", -1), ("room", 4)])
+def test_fused_accumulate_add_equals_the_reduce_of_the_partial_sums(drt, name, variant):
+    """Renderers that own different frame indices and share the root's frame buffers ADD their pixel sums into it with fp32
+    atomics. Two renderers: the buffer holds exactly the fp32 sum of the two partial sums (0 + a + b is a + b in either order),
+    i.e. the bits an ncclReduce of two private buffers gives. Three renderers: the order of the additions is not fixed, the
+    result is within one rounding of the exact sum. The root's resolve gives display = sums / samples. Kernels that cannot add
+    (debug views) refuse."""
+    scene = gpu_scene(drt, name)
+    W, H = 203, 117
+    cam = drt.Camera()
+    st = drt.RendererSettings(enable_sunlight=1, ray_bounce_limit=4, max_samples=100000)
+
+    def make(first, stride, flags=0, add=False):
+        r = drt.Renderer(flags=flags)
+        r.set_tuning(variant, 0)
+        r.m_RendererSettings = st
+        r.ResizeBuffer(W, H)
+        r.set_frame_schedule(first, stride)
+        if add:
+            r.set_accumulate_add(True)
+        return r
+
+    for flags in (STRICT, 0):
+        for world, spp in ((2, 12), (3, 9)):
+            parts = []
+            for g in range(world):
+                r = make(g + 1, world, flags)
+                r.Render(cam, scene, spp)
+                parts.append(r.readback(drt.DRT_ACCUM_RGB32F))
+            root = make(1, world, flags, add=True)
+            peers = [make(g + 1, world, flags, add=True) for g in range(1, world)]
+            for p in peers:
+                p.attach_frame_buffers(root)
+            root.resetAccumulationBuffer()
+            for r in [root] + peers:
+                r.Render(cam, scene, spp)
+            got = root.readback(drt.DRT_ACCUM_RGB32F)
+            if world == 2:
+                assert np.array_equal(bits(got), bits(parts[0] + parts[1])), (flags, "two partial sums")
+            else:
+                exact = sum(p.astype(np.float64) for p in parts)
+                assert np.all(np.abs(got.astype(np.float64) - exact) <= 2.0 * np.spacing(np.abs(exact).astype(np.float32)).astype(np.float64) + 1e-30)
+            root.resolve(world * spp)
+            disp = root.readback(drt.DRT_RGBA32F)
+            assert np.array_equal(bits(disp[..., :3].reshape(-1)), bits((got.reshape(-1) / np.float32(world * spp)).astype(np.float32)))
+    r = make(1, 1, 0, add=True)
+    r.m_RendererSettings = drt.RendererSettings(render_mode=1, debug_mode=1, max_samples=100000)
+    with pytest.raises(drt.DrtError):
+        r.Render(cam, scene, 4)
