@@ -473,7 +473,7 @@ extern "C" int drt_scene_build_bvh(drt_scene* scene, const drt_bvh_params* param
 			ex.launches = 1;
 			res.bvh2_nodes = h_res[0]; res.wide_nodes = h_res[1]; res.levels = h_res[2]; res.wide_levels = h_res[3]; res.tris_emitted = h_res[4];
 #ifdef DRT_BUILD_SMALL_TIMING
-			fprintf(stderr, "k_build_small clocks: init %d", h_res[8]);
+			fprintf(stderr, "k_build_small clocks: warp split max sah %d partition %d | init %d", h_res[6], h_res[7], h_res[8]);
 			for (int l = 0; l < h_res[2] && l < 16; l++) fprintf(stderr, " | L%d bin %d split %d part %d", l, h_res[9 + 3 * l], h_res[10 + 3 * l], h_res[11 + 3 * l]);
 			for (int l = 0; l < h_res[3] && l < 6; l++) fprintf(stderr, " | W%d %d", l, h_res[57 + l]);
 			fprintf(stderr, "\n");

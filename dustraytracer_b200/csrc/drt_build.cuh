@@ -104,11 +104,27 @@ struct BuildArrays {
 	drt_f4* out_tris; drt_f4* out_shade;
 };
 
+// (separately rounded on the device too: the serial sweeps below, the warp-cooperative split of the single-launch builder and the
+// host emulation must take the same decisions, whatever multiply-adds the compiler would contract in each code shape)
 DRT_HD float box_area(float lx, float ly, float lz, float hx, float hy, float hz)
 {
 	float dx = hx - lx, dy = hy - ly, dz = hz - lz;
 	if (!(dx >= 0.f) || !(dy >= 0.f) || !(dz >= 0.f)) return 0.f; // empty box
+#if defined(__CUDA_ARCH__)
+	return __fmul_rn(2.f, __fadd_rn(__fadd_rn(__fmul_rn(dx, dy), __fmul_rn(dy, dz)), __fmul_rn(dz, dx)));
+#else
 	return 2.f * (dx * dy + dy * dz + dz * dx);
+#endif
+}
+
+// SAH cost of a candidate plane: SA(L) n_L + SA(R) n_R
+DRT_HD float sah_cost(float area_l, int n_l, float area_r, int n_r)
+{
+#if defined(__CUDA_ARCH__)
+	return __fadd_rn(__fmul_rn(area_l, (float)n_l), __fmul_rn(area_r, (float)n_r));
+#else
+	return area_l * (float)n_l + area_r * (float)n_r;
+#endif
 }
 
 DRT_HD int bin_of(float c, float cmin, float cmax, int nbins)
@@ -209,7 +225,7 @@ DRT_HD bool best_plane(const BinAcc* bins, int nbins, float& best_cost, int& bes
 		acc_merge(l, bins[s - 1]);
 		const BinAcc& rr = right_acc[s];
 		if (l.n == 0 || rr.n == 0) continue;
-		float cost = acc_area(l) * (float)l.n + acc_area(rr) * (float)rr.n;
+		float cost = sah_cost(acc_area(l), l.n, acc_area(rr), rr.n);
 		if (!found || cost < best_cost) { found = true; best_cost = cost; best_split = s; bestL = l; bestR = rr; }
 	}
 	return found;
@@ -382,14 +398,14 @@ DRT_HD void write_triangle(const BuildArrays& A, int slot, int prim)
 	A.out_shade[3 * (size_t)slot] = s0; A.out_shade[3 * (size_t)slot + 1] = s1; A.out_shade[3 * (size_t)slot + 2] = s2;
 }
 
-// `idx` is the final primitive order (leaf ranges of the BVH2 index into it).
-DRT_HD void collapse_node(const BuildArrays& A, const int* idx, int wide_level_start, int wide_level_end, int j)
+// ---- collapse of one wide node, in three steps (the single-launch builder runs the middle one on a whole warp) ----
+// 1. the children: open the inner child with the largest surface area until there are 8 (or only leaves); their costs per slot:
+//    slot bit set (x=4,y=2,z=1) <=> child lies on the + side of that axis, so a ray travelling towards + visits slot^7 in
+//    descending order = near to far (drt_trace.cuh)
+DRT_HD int collapse_children(const BuildArrays& A, int w, int* child, float* cost /* [8][8] */)
 {
-	int w = wide_level_start + j;
-	if (w >= wide_level_end) return;
 	const int src = A.wide_src[w];
 	const BuildNode& parent = A.nodes[src];
-	int child[8];
 	int n = 0;
 	if (parent.left < 0) child[n++] = src; // the whole scene is one leaf
 	else { child[n++] = parent.left; child[n++] = parent.left + 1; }
@@ -406,34 +422,43 @@ DRT_HD void collapse_node(const BuildArrays& A, const int* idx, int wide_level_s
 		child[best] = l;
 		child[n++] = l + 1;
 	}
-
-	const float plo[3] = { dec_f(parent.lo[0]), dec_f(parent.lo[1]), dec_f(parent.lo[2]) };
-	const float phi[3] = { dec_f(parent.hi[0]), dec_f(parent.hi[1]), dec_f(parent.hi[2]) };
-	const float pc[3] = { 0.5f * (plo[0] + phi[0]), 0.5f * (plo[1] + phi[1]), 0.5f * (plo[2] + phi[2]) };
-
-	// greedy slot assignment: slot bit set (x=4,y=2,z=1) <=> child lies on the + side of that axis, so a
-	// ray travelling towards + visits slot^7 in descending order = near to far (drt_trace.cuh)
-	int slot_of[8], child_in_slot[8];
-	for (int k = 0; k < 8; k++) { slot_of[k] = -1; child_in_slot[k] = -1; }
-	float cost[8][8];
+	const float pc[3] = { 0.5f * (dec_f(parent.lo[0]) + dec_f(parent.hi[0])), 0.5f * (dec_f(parent.lo[1]) + dec_f(parent.hi[1])), 0.5f * (dec_f(parent.lo[2]) + dec_f(parent.hi[2])) };
 	for (int k = 0; k < n; k++) {
 		const BuildNode& c = A.nodes[child[k]];
 		float d[3];
 		for (int a = 0; a < 3; a++) d[a] = 0.5f * (dec_f(c.lo[a]) + dec_f(c.hi[a])) - pc[a];
 		for (int s = 0; s < 8; s++)
-			cost[k][s] = ((s & 4) ? d[0] : -d[0]) + ((s & 2) ? d[1] : -d[1]) + ((s & 1) ? d[2] : -d[2]);
+			cost[k * 8 + s] = ((s & 4) ? d[0] : -d[0]) + ((s & 2) ? d[1] : -d[1]) + ((s & 1) ? d[2] : -d[2]);
 	}
+	return n;
+}
+
+// 2. greedy slot assignment: the free (child, slot) pair of largest cost, ties to the first pair in (child, slot) order, n times
+DRT_HD void collapse_match(int n, const float* cost, int* slot_of, int* child_in_slot)
+{
+	for (int k = 0; k < 8; k++) { slot_of[k] = -1; child_in_slot[k] = -1; }
 	for (int it = 0; it < n; it++) {
 		int bk = -1, bs = -1; float bc = -INFINITY;
 		for (int k = 0; k < n; k++) {
 			if (slot_of[k] >= 0) continue;
 			for (int s = 0; s < 8; s++) {
 				if (child_in_slot[s] >= 0) continue;
-				if (bk < 0 || cost[k][s] > bc) { bc = cost[k][s]; bk = k; bs = s; }
+				if (bk < 0 || cost[k * 8 + s] > bc) { bc = cost[k * 8 + s]; bk = k; bs = s; }
 			}
 		}
 		slot_of[bk] = bs; child_in_slot[bs] = bk;
 	}
+}
+
+// 3. the node: child / triangle ranges, quantised child boxes, triangles in leaf order. `idx` is the final primitive order (leaf
+// ranges of the BVH2 index into it). `defer`, when given, receives the node's triangle copies instead of having them done here:
+// defer[0] = their number (<= 24), then (output slot, primitive) pairs -- the single-launch builder lets the lanes of a warp do
+// them side by side (a copy is 18 dependent loads + 6 stores).
+DRT_HD void collapse_emit(const BuildArrays& A, const int* idx, int w, const int* child, int n, const int* child_in_slot, int* defer)
+{
+	const BuildNode& parent = A.nodes[A.wide_src[w]];
+	const float plo[3] = { dec_f(parent.lo[0]), dec_f(parent.lo[1]), dec_f(parent.lo[2]) };
+	const float phi[3] = { dec_f(parent.hi[0]), dec_f(parent.hi[1]), dec_f(parent.hi[2]) };
 
 	int n_inner = 0, n_tris = 0;
 	for (int k = 0; k < n; k++) {
@@ -489,11 +514,25 @@ DRT_HD void collapse_node(const BuildArrays& A, const int* idx, int wide_level_s
 		else {
 			const uint32_t unary = c.count == 1 ? 1u : (c.count == 2 ? 3u : 7u);
 			out.meta[s] = (uint8_t)((unary << 5) | (uint32_t)tri_off);
-			for (int t = 0; t < c.count; t++) write_triangle(A, tri_base + tri_off + t, idx[c.start + t]);
+			for (int t = 0; t < c.count; t++) {
+				if (defer) { const int k2 = defer[0]++; defer[1 + 2 * k2] = tri_base + tri_off + t; defer[2 + 2 * k2] = idx[c.start + t]; }
+				else write_triangle(A, tri_base + tri_off + t, idx[c.start + t]);
+			}
 			tri_off += c.count;
 		}
 	}
 	A.wide[w] = out;
+}
+
+DRT_HD void collapse_node(const BuildArrays& A, const int* idx, int wide_level_start, int wide_level_end, int j, int* defer = nullptr)
+{
+	int w = wide_level_start + j;
+	if (w >= wide_level_end) return;
+	int child[8], slot_of[8], child_in_slot[8];
+	float cost[64];
+	const int n = collapse_children(A, w, child, cost);
+	collapse_match(n, cost, slot_of, child_in_slot);
+	collapse_emit(A, idx, w, child, n, child_in_slot, defer);
 }
 
 } // namespace drt

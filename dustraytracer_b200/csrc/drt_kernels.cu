@@ -778,6 +778,255 @@ cudaError_t launch_expand_nodes(const WideNode* wide, drt_f4* out, int n, cudaSt
 	return cudaGetLastError();
 }
 
+// One WARP splits one small node (count <= DRT_SMALL_NODE = 32 primitives), in registers: lane k holds primitive k. Per axis the
+// lanes add their boxes to the bins in shared memory (atomics on the order-preserving integer encoding of the bounds), lanes
+// 0 .. 15 pick one bin each, a prefix and a suffix scan over those lanes (shuffles) give every candidate
+// plane's two sides at once, lane s evaluates plane s, and one redux picks the cheapest. It takes the decisions of split_node's
+// small path (drt_build.cuh) -- a union of boxes does not depend on the order, the costs are the same separately rounded expression
+// on the same values, ties go to the first axis / first plane -- where one thread needs ~35 k clocks because its bin arrays live in
+// local memory. `bins` = DRT_SMALL_BINS x 7 words of shared memory owned by this warp.
+#ifdef DRT_BUILD_SMALL_TIMING
+__device__ int* g_bs_debug = nullptr; // result + 6: max clocks of the SAH part / the partition part of a warp split
+#endif
+struct WarpBin { int n; float lo[3], hi[3]; };
+__device__ __forceinline__ void warp_bin_merge(WarpBin& d, const WarpBin& o)
+{
+	d.n += o.n;
+#pragma unroll
+	for (int k = 0; k < 3; k++) { d.lo[k] = fminf(d.lo[k], o.lo[k]); d.hi[k] = fmaxf(d.hi[k], o.hi[k]); }
+}
+__device__ __forceinline__ WarpBin warp_bin_shfl(const WarpBin& v, int src_lane)
+{
+	WarpBin o;
+	o.n = __shfl_sync(0xffffffffu, v.n, src_lane);
+#pragma unroll
+	for (int k = 0; k < 3; k++) { o.lo[k] = __shfl_sync(0xffffffffu, v.lo[k], src_lane); o.hi[k] = __shfl_sync(0xffffffffu, v.hi[k], src_lane); }
+	return o;
+}
+// Lane b < NB holds bin b of one axis (the other lanes an empty bin). Inclusive prefix and suffix unions over the bins (shuffles), lane s
+// evaluates plane s (bins 0 .. s-1 | bins s .. NB-1), one redux finds the cheapest plane; kmin = its cost bits (0xffffffff: every plane leaves a
+// side empty), split = the first plane among the cheapest, bl / br = its two sides (on every lane).
+template <int NB>
+__device__ __forceinline__ void warp_plane_search(const WarpBin& v, int lane, unsigned& kmin, int& split, WarpBin& bl, WarpBin& br)
+{
+	const unsigned FULL = 0xffffffffu;
+	WarpBin pre = v, suf = v;
+#pragma unroll
+	for (int d = 1; d < NB; d <<= 1) {
+		const WarpBin up = warp_bin_shfl(pre, lane - d >= 0 ? lane - d : lane), dn = warp_bin_shfl(suf, lane + d < 32 ? lane + d : lane);
+		if (lane >= d) warp_bin_merge(pre, up);
+		if (lane + d < NB) warp_bin_merge(suf, dn);
+	}
+	const WarpBin L = warp_bin_shfl(pre, lane >= 1 ? lane - 1 : 0);
+	unsigned key = 0xffffffffu; // cost bits of a valid plane (costs are >= 0: unsigned order = float order)
+	if (lane >= 1 && lane < NB && L.n > 0 && suf.n > 0)
+		key = __float_as_uint(sah_cost(box_area(L.lo[0], L.lo[1], L.lo[2], L.hi[0], L.hi[1], L.hi[2]), L.n,
+		                               box_area(suf.lo[0], suf.lo[1], suf.lo[2], suf.hi[0], suf.hi[1], suf.hi[2]), suf.n));
+	kmin = __reduce_min_sync(FULL, key);
+	split = kmin != 0xffffffffu ? __ffs(__ballot_sync(FULL, key == kmin)) - 1 : 0;
+	bl = warp_bin_shfl(L, split);
+	br = warp_bin_shfl(suf, split);
+}
+
+// Greedy slot assignment of collapse_match (drt_build.cuh) on a warp: lane l owns the pairs 2l and 2l + 1 (pair = child * 8 + slot).
+// Every round: the largest cost among the free pairs (redux max on the order-preserving encoding; -0 counts as +0, as it does for
+// the serial `>`), then the first pair that has it (redux min) -- the serial loop's choice.
+#define DRT_BS_WARP_SCRATCH 144
+__device__ __forceinline__ void warp_collapse_match(int n, const float* cost, int* slot_of, int* child_in_slot)
+{
+	const unsigned FULL = 0xffffffffu;
+	const int lane = (int)(threadIdx.x & 31u);
+	int key[2];
+#pragma unroll
+	for (int t = 0; t < 2; t++) {
+		const float c = cost[2 * lane + t];
+		key[t] = ((2 * lane + t) >> 3) < n ? enc_f(c == 0.f ? 0.f : c) : INT_MIN;
+	}
+	unsigned free_k = (1u << n) - 1u, free_s = 0xffu;
+	if (lane < 8) { slot_of[lane] = -1; child_in_slot[lane] = -1; }
+	for (int it = 0; it < n; it++) {
+		int best = INT_MIN;
+#pragma unroll
+		for (int t = 0; t < 2; t++) {
+			const int p = 2 * lane + t;
+			if (((free_k >> (p >> 3)) & 1u) && ((free_s >> (p & 7)) & 1u) && key[t] > best) best = key[t];
+		}
+		const int wmax = __reduce_max_sync(FULL, best);
+		int first = 64;
+#pragma unroll
+		for (int t = 1; t >= 0; t--) {
+			const int p = 2 * lane + t;
+			if (((free_k >> (p >> 3)) & 1u) && ((free_s >> (p & 7)) & 1u) && key[t] == wmax) first = p;
+		}
+		const int p = __reduce_min_sync(FULL, first);
+		const int bk = p >> 3, bs = p & 7;
+		free_k &= ~(1u << bk); free_s &= ~(1u << bs);
+		if (lane == 0) { slot_of[bk] = bs; child_in_slot[bs] = bk; }
+	}
+}
+
+// One warp splits one LARGE node (its bins were filled by the binning pass): the decisions of split_node's large path, with the
+// sweep over the DRT_BINS bins of an axis done by warp_plane_search instead of one thread's loop over local-memory arrays.
+__device__ __forceinline__ void split_large_node_warp(const BuildArrays& A, int node)
+{
+	const int lane = (int)(threadIdx.x & 31u);
+	BuildNode* nd = A.nodes + node;
+	const int count = nd->count, start = nd->start;
+	int best_axis = -1, best_split = 0;
+	float best_cost = 0.f;
+	WarpBin bestL, bestR;
+	bestL.n = bestR.n = 0;
+	for (int k = 0; k < 3; k++) { bestL.lo[k] = bestR.lo[k] = INFINITY; bestL.hi[k] = bestR.hi[k] = -INFINITY; }
+	if (A.level < DRT_MEDIAN_LEVEL) {
+		const int* nb = A.bins + (size_t)(A.splits[node].bin_slot - A.bin_slot_base) * 3 * DRT_BINS * DRT_BIN_WORDS;
+#pragma unroll
+		for (int a = 0; a < 3; a++) {
+			WarpBin v;
+			v.n = 0; v.lo[0] = v.lo[1] = v.lo[2] = INFINITY; v.hi[0] = v.hi[1] = v.hi[2] = -INFINITY;
+			if (lane < DRT_BINS) {
+				const int* w = nb + (a * DRT_BINS + lane) * DRT_BIN_WORDS;
+				v.n = w[0];
+				for (int k = 0; k < 3; k++) { v.lo[k] = dec_f(w[1 + k]); v.hi[k] = dec_f(w[4 + k]); }
+			}
+			unsigned kmin;
+			int split;
+			WarpBin bl, br;
+			warp_plane_search<DRT_BINS>(v, lane, kmin, split, bl, br);
+			if (kmin != 0xffffffffu) {
+				const float cost = __uint_as_float(kmin);
+				if (best_axis < 0 || cost < best_cost) { best_axis = a; best_cost = cost; best_split = split; bestL = bl; bestR = br; }
+			}
+		}
+	}
+	if (lane == 0) {
+		const int n_left = best_axis >= 0 ? bestL.n : count / 2;
+		const int c0 = atomic_add_i(&A.state->node_count, 2);
+		BuildNode* L = A.nodes + c0;
+		BuildNode* R = L + 1;
+		init_node(L, start, n_left);
+		init_node(R, start + n_left, count - n_left);
+		if (best_axis >= 0) {
+			for (int k = 0; k < 3; k++) { L->lo[k] = enc_f(bestL.lo[k]); L->hi[k] = enc_f(bestL.hi[k]); R->lo[k] = enc_f(bestR.lo[k]); R->hi[k] = enc_f(bestR.hi[k]); }
+		}
+		BuildSplit sp = A.splits[node];
+		sp.axis = best_axis; sp.split_bin = best_split; sp.n_left = n_left;
+		A.splits[node] = sp;
+		nd->left = c0;
+		for (int k = 0; k < 2; k++) {
+			BuildSplit cs;
+			cs.axis = -1; cs.split_bin = 0; cs.n_left = 0;
+			cs.bin_slot = A.nodes[c0 + k].count > DRT_SMALL_NODE ? atomic_add_i(&A.state->bin_slots, 1) : -1;
+			A.splits[c0 + k] = cs;
+		}
+	}
+}
+
+__device__ __forceinline__ void split_small_node_warp(const BuildArrays& A, int node, int* bins)
+{
+	const unsigned FULL = 0xffffffffu;
+	const int lane = (int)(threadIdx.x & 31u);
+	BuildNode* nd = A.nodes + node;
+	const int count = nd->count, start = nd->start;
+	if (count <= DRT_LEAF_MAX) { if (lane == 0) nd->left = -1; return; }
+	const bool force_median = A.level >= DRT_MEDIAN_LEVEL;
+	const float clo[3] = { dec_f(nd->clo[0]), dec_f(nd->clo[1]), dec_f(nd->clo[2]) };
+	const float chi[3] = { dec_f(nd->chi[0]), dec_f(nd->chi[1]), dec_f(nd->chi[2]) };
+	const bool have = lane < count;
+	int prim = 0;
+	drt_f4 lo, hi;
+	lo.x = lo.y = lo.z = 0.f; hi.x = hi.y = hi.z = 0.f; lo.w = hi.w = 0.f;
+	if (have) { prim = A.idx_in[start + lane]; lo = A.tri_lo[prim]; hi = A.tri_hi[prim]; }
+	const float c[3] = { 0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z) };
+	const int e[6] = { enc_f(lo.x), enc_f(lo.y), enc_f(lo.z), enc_f(hi.x), enc_f(hi.y), enc_f(hi.z) };
+#ifdef DRT_BUILD_SMALL_TIMING
+	const long long wt0 = clock64();
+#endif
+
+	int best_axis = -1, best_split = 0, best_bin = 0;
+	float best_cost = 0.f;
+	if (!force_median) {
+#pragma unroll
+		for (int a = 0; a < 3; a++) {
+			const int bin = have ? bin_of(c[a], clo[a], chi[a], DRT_SMALL_BINS) : 0;
+			// boxes of the bins: shared-memory atomics of the lanes that hold a primitive (a segmented redux -- match.any + redux per
+			// group of lanes -- runs once per distinct group and measured 15 k clocks per axis)
+			if (lane < DRT_SMALL_BINS) {
+				int* w = bins + lane * 7;
+				w[0] = 0; w[1] = w[2] = w[3] = DRT_ENC_POS_INF; w[4] = w[5] = w[6] = DRT_ENC_NEG_INF;
+			}
+			__syncwarp();
+			if (have) {
+				int* w = bins + bin * 7;
+				atomicAdd(w, 1);
+				atomicMin(w + 1, e[0]); atomicMin(w + 2, e[1]); atomicMin(w + 3, e[2]);
+				atomicMax(w + 4, e[3]); atomicMax(w + 5, e[4]); atomicMax(w + 6, e[5]);
+			}
+			__syncwarp();
+			WarpBin v; // lane b < DRT_SMALL_BINS: bin b; the other lanes: empty
+			v.n = 0; v.lo[0] = v.lo[1] = v.lo[2] = INFINITY; v.hi[0] = v.hi[1] = v.hi[2] = -INFINITY;
+			if (lane < DRT_SMALL_BINS) {
+				const int* w = bins + lane * 7;
+				v.n = w[0];
+				for (int k = 0; k < 3; k++) { v.lo[k] = dec_f(w[1 + k]); v.hi[k] = dec_f(w[4 + k]); }
+			}
+			__syncwarp();
+			unsigned kmin;
+			int split;
+			WarpBin bl, br;
+			warp_plane_search<DRT_SMALL_BINS>(v, lane, kmin, split, bl, br);
+			if (kmin != 0xffffffffu) {
+				const float cost = __uint_as_float(kmin);
+				if (best_axis < 0 || cost < best_cost) { best_axis = a; best_cost = cost; best_split = split; best_bin = bin; }
+			}
+		}
+	}
+#ifdef DRT_BUILD_SMALL_TIMING
+	const long long wt1 = clock64();
+#endif
+	// partition (stable on both sides, like the serial code) and the children's exact boxes
+	const bool left = have && (best_axis >= 0 ? best_bin < best_split : lane < count / 2);
+	const unsigned lm = __ballot_sync(FULL, left), rm = __ballot_sync(FULL, have && !left);
+	const int nl = __popc(lm), nr = __popc(rm);
+	int c0 = 0;
+	if (lane == 0) c0 = atomic_add_i(&A.state->node_count, 2);
+	c0 = __shfl_sync(FULL, c0, 0);
+	if (have) {
+		const unsigned m = left ? lm : rm;
+		const int ec[3] = { enc_f(c[0]), enc_f(c[1]), enc_f(c[2]) };
+		int b[6], cc[6];
+#pragma unroll
+		for (int k = 0; k < 3; k++) {
+			b[k] = __reduce_min_sync(m, e[k]); b[3 + k] = __reduce_max_sync(m, e[3 + k]);
+			cc[k] = __reduce_min_sync(m, ec[k]); cc[3 + k] = __reduce_max_sync(m, ec[k]);
+		}
+		const int side = left ? 0 : 1;
+		if (lane == __ffs(m) - 1) {
+			BuildNode* ch = A.nodes + c0 + side;
+			for (int k = 0; k < 3; k++) { ch->lo[k] = b[k]; ch->hi[k] = b[3 + k]; ch->clo[k] = cc[k]; ch->chi[k] = cc[3 + k]; }
+			ch->start = left ? start : start + nl;
+			ch->count = left ? nl : nr;
+			ch->left = -1;
+			ch->fill = left ? nl : nr;
+			BuildSplit cs;
+			cs.axis = -1; cs.split_bin = 0; cs.n_left = 0; cs.bin_slot = -1; // (the children of a small node are small)
+			A.splits[c0 + side] = cs;
+		}
+		const unsigned below = (1u << lane) - 1u;
+		const int pos = left ? __popc(lm & below) : nl + __popc(rm & below);
+		A.idx_in[start + pos] = prim;
+		A.pnode_in[start + pos] = c0 + side;
+	}
+	if (lane == 0) {
+		BuildSplit sp = A.splits[node];
+		sp.axis = best_axis; sp.split_bin = best_split; sp.n_left = nl;
+		A.splits[node] = sp;
+		nd->left = c0;
+	}
+#ifdef DRT_BUILD_SMALL_TIMING
+	if (lane == 0 && g_bs_debug) { atomicMax(&g_bs_debug[0], (int)(wt1 - wt0)); atomicMax(&g_bs_debug[1], (int)(clock64() - wt1)); }
+#endif
+}
+
 // The whole build of a SMALL scene in ONE launch (one block): the level loop of run_build (drt_build_driver.h) with block
 // barriers where the host loop has kernel boundaries and the BuildState words read back through shared memory instead of a
 // host round trip per level. Same per-index passes, hence the same tree; the level-synchronous path spends ~60 launches and a
@@ -786,8 +1035,13 @@ cudaError_t launch_expand_nodes(const WideNode* wide, drt_f4* out, int n, cudaSt
 __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(const BuildArrays A0, int* result)
 {
 	__shared__ int s_count[2];
+	__shared__ int s_warp_scratch[(DRT_BUILD_SMALL_THREADS / 32) * DRT_BS_WARP_SCRATCH]; // per warp: the bins of a small-node split / the collapse's arrays
 	BuildArrays A = A0;
 	const int tid = (int)threadIdx.x, nt = (int)blockDim.x, n = A.n;
+#ifdef DRT_BUILD_SMALL_TIMING
+	if (tid == 0) { g_bs_debug = result + 6; result[6] = result[7] = 0; }
+	__syncthreads();
+#endif
 	if (tid == 0) {
 		init_node(&A.nodes[0], 0, n);
 		BuildSplit rs;
@@ -819,10 +1073,12 @@ __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(cons
 			__syncthreads();
 		}
 		DRT_BS_TICK(9 + 3 * level);
-		// (one thread per node, nodes packed into as few warps as possible: the split is a long serial routine working in local
-		// memory; dealing the nodes to 32 warps instead -- one or a few active lanes per warp -- measured 1.6x SLOWER, because a
-		// warp's local-memory lines are then fetched for single lanes and 1024 threads' local arrays fall out of L1)
-		for (int j = tid; j < level_end - level_start; j += nt) split_node(A, j);
+		// one warp per node, in registers: small nodes (<= 32 primitives) bin their own primitives, large nodes read the bins the
+		// pass above filled
+		for (int j = tid >> 5; j < level_end - level_start; j += nt >> 5) {
+			if (A.nodes[level_start + j].count <= DRT_SMALL_NODE) split_small_node_warp(A, level_start + j, s_warp_scratch + (tid >> 5) * DRT_BS_WARP_SCRATCH);
+			else split_large_node_warp(A, level_start + j);
+		}
 		__syncthreads();
 		DRT_BS_TICK(10 + 3 * level);
 		for (int i = tid; i < n; i += nt) partition_prim(A, i);
@@ -841,7 +1097,25 @@ __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(cons
 	const int bvh2_nodes = level_end;
 	int ws = 0, we = 1, wl = 0;
 	while (we > ws) {
-		for (int j = tid; j < we - ws; j += nt) collapse_node(A, A.idx_in, ws, we, j);
+		// one warp per wide node, its scratch in shared memory: lane 0 collects the children and their slot costs, the warp does
+		// the greedy slot assignment (64 pairs on 32 lanes, two redux per round; one thread needs 8 x 64 dependent local-memory
+		// reads), lane 0 emits the node and lists its triangle copies, the lanes copy one triangle each
+		for (int j = tid >> 5; j < we - ws; j += nt >> 5) {
+			int* scr = s_warp_scratch + (tid >> 5) * DRT_BS_WARP_SCRATCH;
+			int* child = scr, * slot_of = scr + 8, * child_in_slot = scr + 16, * jobs = scr + 24; // 8 + 8 + 8 + 49 ints
+			float* cost = (float*)(scr + 80);                                                  // 64 floats
+			const int lane = (int)(tid & 31);
+			int n = 0;
+			if (lane == 0) n = collapse_children(A, ws + j, child, cost);
+			n = __shfl_sync(0xffffffffu, n, 0);
+			__syncwarp();
+			warp_collapse_match(n, cost, slot_of, child_in_slot);
+			__syncwarp();
+			if (lane == 0) { jobs[0] = 0; collapse_emit(A, A.idx_in, ws + j, child, n, child_in_slot, jobs); }
+			__syncwarp();
+			if (lane < jobs[0]) write_triangle(A, jobs[1 + 2 * lane], jobs[2 + 2 * lane]);
+			__syncwarp();
+		}
 		__syncthreads();
 		DRT_BS_TICK(57 + wl);
 		if (tid == 0) s_count[0] = A.state->wide_count;
@@ -857,10 +1131,9 @@ __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(cons
 cudaError_t launch_build_small(const BuildArrays& A, int* result, cudaStream_t s)
 {
 	if (A.n <= 0) return cudaErrorInvalidValue;
-	// one thread per primitive up to the block limit (the passes are strided loops; fewer threads = cheaper barriers and less
-	// local memory competing for L1)
+	// one thread per primitive, and warps enough for the nodes of a level (one warp per small node): at least 16 warps
 	int threads = ((A.n + 31) / 32) * 32;
-	if (threads < 64) threads = 64;
+	if (threads < 512) threads = 512;
 	if (threads > DRT_BUILD_SMALL_THREADS) threads = DRT_BUILD_SMALL_THREADS;
 	static const char* env = getenv("DRT_BUILD_SMALL_BLOCK"); // measurement override
 	if (env && atoi(env) >= 32 && atoi(env) <= DRT_BUILD_SMALL_THREADS) threads = (atoi(env) / 32) * 32;
