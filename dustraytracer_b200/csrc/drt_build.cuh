@@ -450,6 +450,35 @@ DRT_HD void collapse_match(int n, const float* cost, int* slot_of, int* child_in
 	}
 }
 
+// quantisation grid of a wide node: per axis the smallest power-of-two step with which 255 steps from the box's low corner reach its high corner
+DRT_HD void quant_grid(const float* plo, const float* phi, uint32_t* e, float* scale)
+{
+	for (int a = 0; a < 3; a++) {
+		e[a] = quant_exponent(phi[a] - plo[a]);
+		// make sure hi is reachable with q <= 255 after the outward rounding below
+		for (;;) {
+			scale[a] = as_float(e[a] << 23);
+			if (plo[a] + 255.f * scale[a] >= phi[a] || e[a] >= 254u) break;
+			e[a]++;
+		}
+	}
+}
+// a child's box on that grid, rounded outward
+DRT_HD void quant_child(const BuildNode& c, const float* plo, const float* scale, uint32_t* ql, uint32_t* qh)
+{
+	for (int a = 0; a < 3; a++) {
+		float lo = dec_f(c.lo[a]), hi = dec_f(c.hi[a]);
+		float base = plo[a];
+		int q0 = (int)floorf((lo - base) / scale[a]);
+		int q1 = (int)ceilf((hi - base) / scale[a]);
+		q0 = q0 < 0 ? 0 : (q0 > 255 ? 255 : q0);
+		q1 = q1 < 0 ? 0 : (q1 > 255 ? 255 : q1);
+		while (q0 > 0 && base + (float)q0 * scale[a] > lo) q0--;    // outward rounding, verified in fp32
+		while (q1 < 255 && base + (float)q1 * scale[a] < hi) q1++;
+		ql[a] = (uint32_t)q0; qh[a] = (uint32_t)q1;
+	}
+}
+
 // 3. the node: child / triangle ranges, quantised child boxes, triangles in leaf order. `idx` is the final primitive order (leaf
 // ranges of the BVH2 index into it). `defer`, when given, receives the node's triangle copies instead of having them done here:
 // defer[0] = their number (<= 24), then (output slot, primitive) pairs -- the single-launch builder lets the lanes of a warp do
@@ -472,15 +501,7 @@ DRT_HD void collapse_emit(const BuildArrays& A, const int* idx, int w, const int
 	out.px = plo[0]; out.py = plo[1]; out.pz = plo[2];
 	uint32_t e[3];
 	float scale[3];
-	for (int a = 0; a < 3; a++) {
-		e[a] = quant_exponent(phi[a] - plo[a]);
-		// make sure hi is reachable with q <= 255 after the outward rounding below
-		for (;;) {
-			scale[a] = as_float(e[a] << 23);
-			if (plo[a] + 255.f * scale[a] >= phi[a] || e[a] >= 254u) break;
-			e[a]++;
-		}
-	}
+	quant_grid(plo, phi, e, scale);
 	out.ex = (uint8_t)e[0]; out.ey = (uint8_t)e[1]; out.ez = (uint8_t)e[2];
 	out.imask = 0; out.child_base = (uint32_t)child_base; out.tri_base = (uint32_t)tri_base;
 	int inner_rank = 0, tri_off = 0;
@@ -491,20 +512,10 @@ DRT_HD void collapse_emit(const BuildArrays& A, const int* idx, int w, const int
 		int k = child_in_slot[s];
 		if (k < 0) continue;
 		const BuildNode& c = A.nodes[child[k]];
-		uint8_t ql[3], qh[3];
-		for (int a = 0; a < 3; a++) {
-			float lo = dec_f(c.lo[a]), hi = dec_f(c.hi[a]);
-			float base = a == 0 ? out.px : (a == 1 ? out.py : out.pz);
-			int q0 = (int)floorf((lo - base) / scale[a]);
-			int q1 = (int)ceilf((hi - base) / scale[a]);
-			q0 = q0 < 0 ? 0 : (q0 > 255 ? 255 : q0);
-			q1 = q1 < 0 ? 0 : (q1 > 255 ? 255 : q1);
-			while (q0 > 0 && base + (float)q0 * scale[a] > lo) q0--;    // outward rounding, verified in fp32
-			while (q1 < 255 && base + (float)q1 * scale[a] < hi) q1++;
-			ql[a] = (uint8_t)q0; qh[a] = (uint8_t)q1;
-		}
-		out.qlox[s] = ql[0]; out.qloy[s] = ql[1]; out.qloz[s] = ql[2];
-		out.qhix[s] = qh[0]; out.qhiy[s] = qh[1]; out.qhiz[s] = qh[2];
+		uint32_t ql[3], qh[3];
+		quant_child(c, plo, scale, ql, qh);
+		out.qlox[s] = (uint8_t)ql[0]; out.qloy[s] = (uint8_t)ql[1]; out.qloz[s] = (uint8_t)ql[2];
+		out.qhix[s] = (uint8_t)qh[0]; out.qhiy[s] = (uint8_t)qh[1]; out.qhiz[s] = (uint8_t)qh[2];
 		if (c.left >= 0) {
 			out.imask |= (uint8_t)(1u << s);
 			out.meta[s] = (uint8_t)(0x20u | (24u + (uint32_t)s));

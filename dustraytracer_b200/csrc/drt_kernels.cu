@@ -865,6 +865,118 @@ __device__ __forceinline__ void warp_collapse_match(int n, const float* cost, in
 	}
 }
 
+// collapse_children (drt_build.cuh) on a warp: lane k < 8 holds child k (its BVH2 node, whether it is inner, its surface area); the inner
+// child with the largest area (redux max on the area bits, -1 for leaves; ties to the lowest k like the serial `>`) is replaced by its two
+// children until there are 8 or only leaves; then lane k writes child[k] and its eight slot costs.
+__device__ __forceinline__ int warp_collapse_children(const BuildArrays& A, int w, int* child, float* cost)
+{
+	const unsigned FULL = 0xffffffffu;
+	const int lane = (int)(threadIdx.x & 31u);
+	const int src = A.wide_src[w];
+	const BuildNode& parent = A.nodes[src];
+	const int pleft = parent.left;
+	int n = pleft < 0 ? 1 : 2;
+	int my = -1, my_left = -1, key = -1; // BVH2 node of this lane's child, its left child, area bits (inner) or -1 (leaf / none)
+	if (lane < n) my = pleft < 0 ? src : pleft + lane;
+	bool reload = lane < n;
+	for (;;) {
+		if (reload) {
+			const BuildNode& c = A.nodes[my];
+			my_left = c.left;
+			key = my_left >= 0 ? (int)__float_as_uint(node_area(c)) : -1;
+			reload = false;
+		}
+		if (n >= 8) break;
+		const int wmax = __reduce_max_sync(FULL, lane < n ? key : -1);
+		if (wmax < 0) break;
+		const int best = __ffs(__ballot_sync(FULL, lane < n && key == wmax)) - 1;
+		const int l = __shfl_sync(FULL, my_left, best);
+		if (lane == best) { my = l; reload = true; }
+		if (lane == n) { my = l + 1; reload = true; }
+		n++;
+	}
+	if (lane < n) {
+		child[lane] = my;
+		const BuildNode& c = A.nodes[my];
+		float d[3];
+#pragma unroll
+		for (int a = 0; a < 3; a++) d[a] = 0.5f * (dec_f(c.lo[a]) + dec_f(c.hi[a])) - 0.5f * (dec_f(parent.lo[a]) + dec_f(parent.hi[a]));
+#pragma unroll
+		for (int s = 0; s < 8; s++)
+			cost[lane * 8 + s] = ((s & 4) ? d[0] : -d[0]) + ((s & 2) ? d[1] : -d[1]) + ((s & 1) ? d[2] : -d[2]);
+	}
+	return n;
+}
+
+// collapse_emit (drt_build.cuh) on a warp: lane s < 8 is SLOT s (quantises its child's box, knows whether it is inner and how many
+// triangles it holds), ballot / shuffle prefixes give the ranks the serial loop counts, the 80-byte node is put together in shared
+// memory (`image`, 20 words, 16-byte aligned) and stored by five lanes; jobs[] receives the triangle copies.
+__device__ __forceinline__ void warp_collapse_emit(const BuildArrays& A, const int* idx, int w, const int* child, const int* child_in_slot, int* jobs, uint32_t* image)
+{
+	const unsigned FULL = 0xffffffffu;
+	const int lane = (int)(threadIdx.x & 31u);
+	const BuildNode& parent = A.nodes[A.wide_src[w]];
+	const float plo[3] = { dec_f(parent.lo[0]), dec_f(parent.lo[1]), dec_f(parent.lo[2]) };
+	const float phi[3] = { dec_f(parent.hi[0]), dec_f(parent.hi[1]), dec_f(parent.hi[2]) };
+	uint32_t e[3];
+	float scale[3];
+	quant_grid(plo, phi, e, scale);
+	const int k = lane < 8 ? child_in_slot[lane] : -1;
+	const int node = k >= 0 ? child[k] : -1;
+	bool inner = false;
+	int cnt = 0, cstart = 0;
+	uint32_t ql[3] = { 0u, 0u, 0u }, qh[3] = { 0u, 0u, 0u };
+	if (node >= 0) {
+		const BuildNode& c = A.nodes[node];
+		quant_child(c, plo, scale, ql, qh);
+		inner = c.left >= 0;
+		cnt = inner ? 0 : c.count;
+		cstart = c.start;
+	}
+	const unsigned inner_mask = __ballot_sync(FULL, inner);
+	int tri_off = cnt; // -> exclusive prefix sum of the triangle counts in slot order
+#pragma unroll
+	for (int d = 1; d < 8; d <<= 1) {
+		const int up = __shfl_up_sync(FULL, tri_off, d);
+		if (lane >= d) tri_off += up;
+	}
+	const int n_tris = __shfl_sync(FULL, tri_off, 7);
+	tri_off -= cnt;
+	const int n_inner = __popc(inner_mask);
+	int child_base = 0, tri_base = 0;
+	if (lane == 0) {
+		child_base = n_inner ? atomic_add_i(&A.state->wide_count, n_inner) : 0;
+		tri_base = n_tris ? atomic_add_i(&A.state->tri_cursor, n_tris) : 0;
+	}
+	child_base = __shfl_sync(FULL, child_base, 0);
+	tri_base = __shfl_sync(FULL, tri_base, 0);
+	uint8_t* img = (uint8_t*)image;
+	if (lane == 0) {
+		image[0] = __float_as_uint(plo[0]); image[1] = __float_as_uint(plo[1]); image[2] = __float_as_uint(plo[2]);
+		image[3] = e[0] | (e[1] << 8) | (e[2] << 16) | (inner_mask << 24);
+		image[4] = (uint32_t)child_base; image[5] = (uint32_t)tri_base;
+	}
+	if (lane < 8) {
+		uint32_t meta = 0u;
+		if (node >= 0) {
+			if (inner) {
+				meta = 0x20u | (24u + (uint32_t)lane);
+				A.wide_src[child_base + __popc(inner_mask & ((1u << lane) - 1u))] = node;
+			}
+			else {
+				meta = ((cnt == 1 ? 1u : (cnt == 2 ? 3u : 7u)) << 5) | (uint32_t)tri_off;
+				for (int t = 0; t < cnt; t++) { jobs[1 + 2 * (tri_off + t)] = tri_base + tri_off + t; jobs[2 + 2 * (tri_off + t)] = idx[cstart + t]; }
+			}
+		}
+		img[24 + lane] = (uint8_t)meta;
+		img[32 + lane] = (uint8_t)ql[0]; img[40 + lane] = (uint8_t)ql[1]; img[48 + lane] = (uint8_t)ql[2];
+		img[56 + lane] = (uint8_t)qh[0]; img[64 + lane] = (uint8_t)qh[1]; img[72 + lane] = (uint8_t)qh[2];
+	}
+	if (lane == 0) jobs[0] = n_tris;
+	__syncwarp();
+	if (lane < 5) ((uint4*)(A.wide + w))[lane] = ((const uint4*)image)[lane];
+}
+
 // One warp splits one LARGE node (its bins were filled by the binning pass): the decisions of split_node's large path, with the
 // sweep over the DRT_BINS bins of an axis done by warp_plane_search instead of one thread's loop over local-memory arrays.
 __device__ __forceinline__ void split_large_node_warp(const BuildArrays& A, int node)
@@ -990,31 +1102,38 @@ __device__ __forceinline__ void split_small_node_warp(const BuildArrays& A, int 
 	int c0 = 0;
 	if (lane == 0) c0 = atomic_add_i(&A.state->node_count, 2);
 	c0 = __shfl_sync(FULL, c0, 0);
+	// the children's exact boxes and centroid bounds: shared-memory atomics into two records of 12 words (lo, hi, clo, chi)
+	int* rec = bins + DRT_SMALL_BINS * 7;
+	if (lane < 24) rec[lane] = ((lane % 12) < 3 || ((lane % 12) >= 6 && (lane % 12) < 9)) ? DRT_ENC_POS_INF : DRT_ENC_NEG_INF;
+	__syncwarp();
 	if (have) {
-		const unsigned m = left ? lm : rm;
-		const int ec[3] = { enc_f(c[0]), enc_f(c[1]), enc_f(c[2]) };
-		int b[6], cc[6];
+		int* r = rec + (left ? 0 : 12);
 #pragma unroll
 		for (int k = 0; k < 3; k++) {
-			b[k] = __reduce_min_sync(m, e[k]); b[3 + k] = __reduce_max_sync(m, e[3 + k]);
-			cc[k] = __reduce_min_sync(m, ec[k]); cc[3 + k] = __reduce_max_sync(m, ec[k]);
+			const int ec = enc_f(c[k]);
+			atomicMin(r + k, e[k]); atomicMax(r + 3 + k, e[3 + k]);
+			atomicMin(r + 6 + k, ec); atomicMax(r + 9 + k, ec);
 		}
-		const int side = left ? 0 : 1;
-		if (lane == __ffs(m) - 1) {
-			BuildNode* ch = A.nodes + c0 + side;
-			for (int k = 0; k < 3; k++) { ch->lo[k] = b[k]; ch->hi[k] = b[3 + k]; ch->clo[k] = cc[k]; ch->chi[k] = cc[3 + k]; }
-			ch->start = left ? start : start + nl;
-			ch->count = left ? nl : nr;
-			ch->left = -1;
-			ch->fill = left ? nl : nr;
-			BuildSplit cs;
-			cs.axis = -1; cs.split_bin = 0; cs.n_left = 0; cs.bin_slot = -1; // (the children of a small node are small)
-			A.splits[c0 + side] = cs;
-		}
+	}
+	__syncwarp();
+	if (lane < 2) {
+		const int side = lane;
+		const int* r = rec + 12 * side;
+		BuildNode* ch = A.nodes + c0 + side;
+		for (int k = 0; k < 3; k++) { ch->lo[k] = r[k]; ch->hi[k] = r[3 + k]; ch->clo[k] = r[6 + k]; ch->chi[k] = r[9 + k]; }
+		ch->start = side == 0 ? start : start + nl;
+		ch->count = side == 0 ? nl : nr;
+		ch->left = -1;
+		ch->fill = side == 0 ? nl : nr;
+		BuildSplit cs;
+		cs.axis = -1; cs.split_bin = 0; cs.n_left = 0; cs.bin_slot = -1; // (the children of a small node are small)
+		A.splits[c0 + side] = cs;
+	}
+	if (have) {
 		const unsigned below = (1u << lane) - 1u;
 		const int pos = left ? __popc(lm & below) : nl + __popc(rm & below);
 		A.idx_in[start + pos] = prim;
-		A.pnode_in[start + pos] = c0 + side;
+		A.pnode_in[start + pos] = c0 + (left ? 0 : 1);
 	}
 	if (lane == 0) {
 		BuildSplit sp = A.splits[node];
@@ -1035,7 +1154,7 @@ __device__ __forceinline__ void split_small_node_warp(const BuildArrays& A, int 
 __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(const BuildArrays A0, int* result)
 {
 	__shared__ int s_count[2];
-	__shared__ int s_warp_scratch[(DRT_BUILD_SMALL_THREADS / 32) * DRT_BS_WARP_SCRATCH]; // per warp: the bins of a small-node split / the collapse's arrays
+	__shared__ alignas(16) int s_warp_scratch[(DRT_BUILD_SMALL_THREADS / 32) * DRT_BS_WARP_SCRATCH]; // per warp: the bins of a small-node split / the collapse's arrays
 	BuildArrays A = A0;
 	const int tid = (int)threadIdx.x, nt = (int)blockDim.x, n = A.n;
 #ifdef DRT_BUILD_SMALL_TIMING
@@ -1097,21 +1216,18 @@ __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(cons
 	const int bvh2_nodes = level_end;
 	int ws = 0, we = 1, wl = 0;
 	while (we > ws) {
-		// one warp per wide node, its scratch in shared memory: lane 0 collects the children and their slot costs, the warp does
-		// the greedy slot assignment (64 pairs on 32 lanes, two redux per round; one thread needs 8 x 64 dependent local-memory
-		// reads), lane 0 emits the node and lists its triangle copies, the lanes copy one triangle each
+		// one warp per wide node, its scratch in shared memory: children and slot costs (lane = child), greedy slot assignment (64
+		// pairs on 32 lanes), the node itself (lane = slot) and its triangle copies (lane = triangle)
 		for (int j = tid >> 5; j < we - ws; j += nt >> 5) {
 			int* scr = s_warp_scratch + (tid >> 5) * DRT_BS_WARP_SCRATCH;
 			int* child = scr, * slot_of = scr + 8, * child_in_slot = scr + 16, * jobs = scr + 24; // 8 + 8 + 8 + 49 ints
 			float* cost = (float*)(scr + 80);                                                  // 64 floats
 			const int lane = (int)(tid & 31);
-			int n = 0;
-			if (lane == 0) n = collapse_children(A, ws + j, child, cost);
-			n = __shfl_sync(0xffffffffu, n, 0);
+			const int n = warp_collapse_children(A, ws + j, child, cost);
 			__syncwarp();
 			warp_collapse_match(n, cost, slot_of, child_in_slot);
 			__syncwarp();
-			if (lane == 0) { jobs[0] = 0; collapse_emit(A, A.idx_in, ws + j, child, n, child_in_slot, jobs); }
+			warp_collapse_emit(A, A.idx_in, ws + j, child, child_in_slot, jobs, (uint32_t*)cost); // (the costs are spent: their place takes the node image)
 			__syncwarp();
 			if (lane < jobs[0]) write_triangle(A, jobs[1 + 2 * lane], jobs[2 + 2 * lane]);
 			__syncwarp();
