@@ -831,7 +831,8 @@ __device__ __forceinline__ void warp_plane_search(const WarpBin& v, int lane, un
 // Greedy slot assignment of collapse_match (drt_build.cuh) on a warp: lane l owns the pairs 2l and 2l + 1 (pair = child * 8 + slot).
 // Every round: the largest cost among the free pairs (redux max on the order-preserving encoding; -0 counts as +0, as it does for
 // the serial `>`), then the first pair that has it (redux min) -- the serial loop's choice.
-#define DRT_BS_WARP_SCRATCH 144
+#define DRT_BS_SMEM_BIN_NODES 8
+#define DRT_BS_WARP_SCRATCH 144 /* 16 bins x 7 words + 2 child records of 12 words (small split); 144 words (collapse) */
 __device__ __forceinline__ void warp_collapse_match(int n, const float* cost, int* slot_of, int* child_in_slot)
 {
 	const unsigned FULL = 0xffffffffu;
@@ -1057,11 +1058,12 @@ __device__ __forceinline__ void split_small_node_warp(const BuildArrays& A, int 
 	int best_axis = -1, best_split = 0, best_bin = 0;
 	float best_cost = 0.f;
 	if (!force_median) {
+		// boxes of the bins: shared-memory atomics of the lanes that hold a primitive (a segmented redux -- match.any + redux per group
+		// of lanes -- runs once per distinct group and measured 15 k clocks per axis). One bin area, axis after axis: three areas with
+		// the three scan chains side by side measured the same (6.8 k clocks) and cost 2.5x the shared memory.
 #pragma unroll
 		for (int a = 0; a < 3; a++) {
 			const int bin = have ? bin_of(c[a], clo[a], chi[a], DRT_SMALL_BINS) : 0;
-			// boxes of the bins: shared-memory atomics of the lanes that hold a primitive (a segmented redux -- match.any + redux per
-			// group of lanes -- runs once per distinct group and measured 15 k clocks per axis)
 			if (lane < DRT_SMALL_BINS) {
 				int* w = bins + lane * 7;
 				w[0] = 0; w[1] = w[2] = w[3] = DRT_ENC_POS_INF; w[4] = w[5] = w[6] = DRT_ENC_NEG_INF;
@@ -1154,6 +1156,7 @@ __device__ __forceinline__ void split_small_node_warp(const BuildArrays& A, int 
 __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(const BuildArrays A0, int* result)
 {
 	__shared__ int s_count[2];
+	__shared__ int s_level_bins[DRT_BS_SMEM_BIN_NODES * 3 * DRT_BINS * DRT_BIN_WORDS];
 	__shared__ alignas(16) int s_warp_scratch[(DRT_BUILD_SMALL_THREADS / 32) * DRT_BS_WARP_SCRATCH]; // per warp: the bins of a small-node split / the collapse's arrays
 	BuildArrays A = A0;
 	const int tid = (int)threadIdx.x, nt = (int)blockDim.x, n = A.n;
@@ -1184,6 +1187,9 @@ __global__ void __launch_bounds__(DRT_BUILD_SMALL_THREADS, 1) k_build_small(cons
 	int level_start = 0, level_end = 1, level = 0, slot_base = 0, slot_end = n > DRT_SMALL_NODE ? 1 : 0, swapped = 0;
 	while (level_end > level_start) {
 		A.level_start = level_start; A.level_end = level_end; A.level = level; A.bin_slot_base = slot_base;
+		// the bins of a level with few large nodes live in shared memory (the binning pass is ~7 k atomics on a handful of words:
+		// 8-12 k clocks in global memory); levels with more large nodes use the global array
+		A.bins = (slot_end - slot_base) <= DRT_BS_SMEM_BIN_NODES ? s_level_bins : A0.bins;
 		const int bin_words = (slot_end - slot_base) * 3 * DRT_BINS * DRT_BIN_WORDS;
 		if (bin_words > 0) {
 			for (int j = tid; j < bin_words; j += nt) init_bin_word(A, j, bin_words);
@@ -1250,6 +1256,7 @@ cudaError_t launch_build_small(const BuildArrays& A, int* result, cudaStream_t s
 	// one thread per primitive, and warps enough for the nodes of a level (one warp per small node): at least 16 warps
 	int threads = ((A.n + 31) / 32) * 32;
 	if (threads < 512) threads = 512;
+	if (A.n > 128) threads = DRT_BUILD_SMALL_THREADS; // (levels of more than 16 nodes: one warp each)
 	if (threads > DRT_BUILD_SMALL_THREADS) threads = DRT_BUILD_SMALL_THREADS;
 	static const char* env = getenv("DRT_BUILD_SMALL_BLOCK"); // measurement override
 	if (env && atoi(env) >= 32 && atoi(env) <= DRT_BUILD_SMALL_THREADS) threads = (atoi(env) / 32) * 32;

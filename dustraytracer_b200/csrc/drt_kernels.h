@@ -62,7 +62,7 @@ inline bool variant_honours_block_order(int v) { return (v >= 2 && v <= 8) || v 
 cudaError_t launch_build_pass(BuildPass pass, const BuildArrays& A, const int* idx_final, int a, int b, int n, cudaStream_t s);
 // Single-launch build for small scenes (k_build_small: one block runs the whole level loop). `result` = 6 device ints:
 // bvh2 nodes, wide nodes, levels, wide levels, triangles emitted, 1 if the final index array is A.idx_out.
-#define DRT_BUILD_SMALL_THREADS 512
+#define DRT_BUILD_SMALL_THREADS 1024
 #define DRT_BUILD_SMALL_RESULT_INTS 64 /* 6 used; the rest carries per-pass clocks in DRT_BUILD_SMALL_TIMING measurement builds */
 #ifndef DRT_BUILD_SMALL_MAX_TRIS
 #define DRT_BUILD_SMALL_MAX_TRIS 2048
