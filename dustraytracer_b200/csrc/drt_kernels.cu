@@ -653,6 +653,9 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 			sample_pool_scratch_bytes(tiles, tune.pool) <= cfg.pool_scratch_bytes;
 		if (!ok) { variant = variant == 22 ? 4 : 15; tune.pool = 0; }
 		else {
+			// sticky re-issue threshold: 8 with the pool (re-swept on the pool kernels, profiles/r02f_stick_sweep.jsonl: room 256 spp
+			// 125.8 -> 124.6 ms, animemaid +1.5 %, dense_monkey +1.9 %, valorant_ghost -0.3 % against 6)
+			if (cfg.sched_bias[0] <= 0) tune.stick = 8;
 			if (variant == 22) k_render<STRICT, STATS, 22><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 			else k_render<STRICT, STATS, 23><<<blocks, threads, 0, s>>>(P, cfg.rtl, wpb, tune);
 			DRT_RAN(variant);
