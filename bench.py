@@ -8,9 +8,11 @@ One STEP = one pass of the hot path over one batch: the BASELINE config-3 frame 
 256 samples per pixel, ray_bounce_limit 8, sun shadow rays on -- rendered from a reset accumulation buffer
 by ONE batched launch of the render kernel through the C ABI (drt_renderer_render).
   value : Mrays/s (TraceRay + RayTest calls / device time, CUDA events on the launching stream), scene, camera
-          and frame buffers resident in HBM. Multi-GPU: sample-range sharding, every rank renders its own 256
-          frame indices of the same image (weak scaling: 256*N spp per step) followed by one NCCL reduce of the
-          24.9 MB accumulation buffer to rank 0 inside the timed region.
+          and frame buffers resident in HBM. Multi-GPU (default, strong scaling): ONE 256-spp frame per step, rank g
+          renders the frame indices g+1, g+1+N, ... (256/N samples per pixel), then one NCCL reduce of the 33 MB
+          accumulation buffer to rank 0 and the resolve, all inside the timed region. --scaling weak: 256 spp per
+          GPU per step. --shard tiles | p2p | fused: image tiles + reduce, image tiles stored into rank 0's buffers
+          over NVLink, sample ranges added into rank 0's buffer by the render kernels (no collective).
   e2e   : the same step through the public API with HOST buffers: camera/settings structs from host memory
           in, the resolved RGBA32F frame read back to pinned host memory, all inside the timed region.
   --impl reference : the reference's own traversal/shade sources compiled host-side (oracle/_ref, or the C
