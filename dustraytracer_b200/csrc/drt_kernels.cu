@@ -644,7 +644,7 @@ cudaError_t launch_render_v(const RenderParams& P, const LaunchConfig& cfg, cuda
 	// automatic selection: launches of DRT_POOL_MIN_SPP samples or more on scenes of DRT_POOL_MIN_TRIS triangles or more run the
 	// sample-pool form of the kernel (variants 22 / 23) when the renderer has provided the scratch array
 	if (cfg.auto_variant && (variant == 4 || variant == 15) && P.n_samples >= DRT_POOL_MIN_SPP && P.scene.num_tris >= DRT_POOL_MIN_TRIS &&
-		P.pool_scratch != nullptr) variant = variant == 4 ? 22 : 23;
+		P.pool_scratch != nullptr) variant = (variant == 15 || P.scene.num_tris >= DRT_POOL_TRI2_MIN_TRIS) ? 23 : 22; // (with the pool the two-triangle step pays from 256 triangles: room.glb +1.1 %)
 	if ((variant == 17 || variant == 18) && (P.scene.nodes_f32 == nullptr || threads != 128)) variant = variant == 17 ? 4 : 15; // (shared-memory stack: fp32 nodes, 128 threads)
 	if (variant == 22 || variant == 23) {
 		// sample pool: needs the scratch array (one float4 per pool sample of every owned tile), fp32 nodes, 128 threads

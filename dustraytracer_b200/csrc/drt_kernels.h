@@ -27,6 +27,9 @@ namespace drt {
 #ifndef DRT_POOL_MIN_TRIS
 #define DRT_POOL_MIN_TRIS 128
 #endif
+#ifndef DRT_POOL_TRI2_MIN_TRIS
+#define DRT_POOL_TRI2_MIN_TRIS 256 /* pool launches: two-triangle TRI step from this many triangles (measured on the final build: room.glb, 330 triangles, 124.7 -> 123.3 ms at 256 spp, 16.11 -> 15.96 ms at 32 spp; sunshadow_test, 102 triangles, -0.3 %) */
+#endif
 // Upper bound of the scratch array the renderer allocates for the pool on its own (pixels x R x 16 bytes; beyond it the
 // launch runs variants 4 / 15).
 #ifndef DRT_POOL_MAX_SCRATCH_BYTES
